@@ -1,0 +1,96 @@
+/*
+ * nnd_b200.h -- C ABI of libnnd_b200.so: brute-force 3-D nearest neighbour /
+ * chamfer ("nnd") forward + backward for NVIDIA B200 (sm_100a).
+ *
+ * This is the drop-in boundary for the reference's native op layer
+ * (dip/torch-nndistance/src/my_lib_cuda.cpp:25-41,44-72 and the launchers
+ * dip/torch-nndistance/src/nnd_cuda.cu:132-162,185-222).  The reference binds
+ * that layer through pybind11 with at::Tensor arguments; here the same calls
+ * are plain pointers + sizes so any host language can bind them (ctypes stub in
+ * INTEGRATION.md; the in-repo binding is pointcloudregistration_b200/_cabi.py).
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers unless the name says host;
+ *   - clouds are row-major [b, n, 3] float32, contiguous (my_lib_cuda.cpp:5);
+ *   - dist is squared L2 (no sqrt, my_lib.cpp:15), idx is int32 (torch_nndistance/__init__.py:19-20);
+ *   - the caller owns every buffer, the library writes in place (nnd_cuda.cu:140-149);
+ *   - `stream` is a cudaStream_t (NULL = legacy default stream, which is what the
+ *     reference always uses, nnd_cuda.cu:152-153);
+ *   - return value: 0 on success, otherwise a cudaError_t value or one of the
+ *     NND_E* codes below.  (The reference returns 1 on success / 0 on failure,
+ *     nnd_cuda.cu:155-161; the torch_nndistance_aten shim maps back to that.)
+ *   - results: idx bit-exact and dist bit-exact vs the reference CPU path
+ *     my_lib.cpp:3-25 (lowest index on ties, no FMA contraction); gradients
+ *     within 1e-5 relative of my_lib.cpp:91-130 (atomic summation order).
+ *   - there is NO CPU fallback in this library.
+ */
+#ifndef NND_B200_H
+#define NND_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NND_EINVAL      10001  /* bad argument (negative size, null pointer, ...)   */
+#define NND_EWORKSPACE  10002  /* workspace too small or misaligned                 */
+#define NND_EDEVICE     10003  /* device is not compute capability 10.x             */
+
+/* Library / build identification, e.g. "nnd_b200 0.1.0 sm_100a". */
+const char *nnd_version(void);
+
+/* Human-readable text for a return code of this library. */
+const char *nnd_error_string(int code);
+
+/* Scratch bytes needed by nnd_forward_cuda_f32 for a [b,n,3] x [b,m,3] problem
+ * (structure-of-arrays copies of both clouds + packed (dist,idx) keys).
+ * The workspace must be 256-byte aligned device memory. */
+size_t nnd_workspace_bytes(int b, int n, int m);
+
+/* Scratch bytes needed by nnd_query_cuda_f32 (one direction). */
+size_t nnd_query_workspace_bytes(int b, int nq, int nt);
+
+/* Replaces nnd_forward_cuda (my_lib_cuda.cpp:25-41) -> NmDistanceKernelLauncher
+ * (nnd_cuda.cu:132-162): both directions.
+ *   dist1[b,n], idx1[b,n] : for every point of xyz1 its nearest point of xyz2
+ *   dist2[b,m], idx2[b,m] : for every point of xyz2 its nearest point of xyz1
+ * m == 0 (resp. n == 0) gives dist = 0, idx = 0 like my_lib.cpp:9-10,21-22. */
+int nnd_forward_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int m,
+                         float *dist1, float *dist2, int32_t *idx1, int32_t *idx2,
+                         void *workspace, size_t workspace_bytes, void *stream);
+
+/* One direction only (the unit the query-sharded multi-GPU path calls):
+ * for every query point its nearest target point. */
+int nnd_query_cuda_f32(const float *query, const float *target, int b, int nq, int nt,
+                       float *dist, int32_t *idx,
+                       void *workspace, size_t workspace_bytes, void *stream);
+
+/* Replaces nnd_backward_cuda (my_lib_cuda.cpp:44-72) -> NmDistanceGradKernelLauncher
+ * (nnd_cuda.cu:185-222).  OVERWRITES gradxyz1[b,n,3] and gradxyz2[b,m,3] (zero
+ * init fused, like the CPU path my_lib.cpp:91-94; the reference CUDA path
+ * accumulates into caller-zeroed buffers, nnd_cuda.cu:199-200 -- identical when
+ * the caller passes zeros, which torch_nndistance/__init__.py:42-43 does). */
+int nnd_backward_cuda_f32(const float *xyz1, const float *xyz2,
+                          const float *graddist1, const float *graddist2,
+                          const int32_t *idx1, const int32_t *idx2,
+                          int b, int n, int m,
+                          float *gradxyz1, float *gradxyz2, void *stream);
+
+/* One term of the backward (the unit the query-sharded multi-GPU path calls):
+ * for query rows [0,nq) with nearest targets idx:  t = 2*graddist*(q - target[idx]);
+ * grad_query[row] += t ; grad_target[idx] -= t.  ACCUMULATES (caller zeroes). */
+int nnd_backward_term_cuda_f32(const float *query, const float *target,
+                               const float *graddist, const int32_t *idx,
+                               int b, int nq, int nt,
+                               float *grad_query, float *grad_target, void *stream);
+
+/* Number of kernels the last forward / backward call on this thread launched
+ * (bench.py's gpu_launches accounting). */
+int nnd_last_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NND_B200_H */

@@ -1,0 +1,64 @@
+"""ctypes binding of libnnd_b200.so (include/nnd_b200.h).
+
+This is the only place Python touches native code on the product path.  If the
+library is missing the import of any compute entry point raises: there is no CPU
+or PyTorch fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_char_p, c_int, c_size_t, c_void_p
+from pathlib import Path
+
+LIB_PATH = Path(__file__).resolve().parent / "libnnd_b200.so"
+
+#: every symbol include/nnd_b200.h declares -> (restype, argtypes)
+SIGNATURES = {
+    "nnd_version": (c_char_p, []),
+    "nnd_error_string": (c_char_p, [c_int]),
+    "nnd_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "nnd_query_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "nnd_forward_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_size_t, c_void_p]),
+    "nnd_query_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                    c_size_t, c_void_p]),
+    "nnd_backward_cuda_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                       c_int, c_void_p, c_void_p, c_void_p]),
+    "nnd_backward_term_cuda_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p,
+                                            c_void_p, c_void_p]),
+    "nnd_last_launch_count": (c_int, []),
+}
+
+_lib = None
+
+
+class NNDLibraryError(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen the library once and type its entry points.  Raises if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise NNDLibraryError(
+            f"{LIB_PATH} is missing. Build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). There is no CPU fallback for nnd.")
+    lib = ctypes.CDLL(str(LIB_PATH))
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the header and the library disagree
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(code: int, what: str) -> None:
+    if code != 0:
+        msg = load().nnd_error_string(code).decode()
+        raise RuntimeError(f"{what} failed: {msg} (code {code})")
+
+
+def version() -> str:
+    return load().nnd_version().decode()

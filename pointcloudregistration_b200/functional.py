@@ -1,0 +1,157 @@
+"""Host-side mirror of the reference's autograd boundary for nnd.
+
+Mirrors dip/torch-nndistance/torch_nndistance/__init__.py:10-61 (NNDFunction,
+nnd) on top of the C ABI in include/nnd_b200.h.  Same names, same argument
+meaning, same 2-tuple return.  Differences, all deliberate:
+outputs are allocated directly on xyz1's device (the reference builds them on
+the CPU and copies, __init__.py:17-28), kernels run on torch's current stream
+(the reference uses the legacy default stream, nnd_cuda.cu:152), inputs are
+validated, and CPU tensors are rejected -- this build has no CPU path.
+"""
+from __future__ import annotations
+
+import torch
+from torch.autograd import Function
+
+from . import _cabi
+
+
+def _check_clouds(xyz1: torch.Tensor, xyz2: torch.Tensor) -> None:
+    for name, t in (("xyz1", xyz1), ("xyz2", xyz2)):
+        if not isinstance(t, torch.Tensor):
+            raise TypeError(f"{name} must be a torch.Tensor")
+        if t.dim() != 3 or t.size(2) != 3:
+            raise ValueError(f"{name} must have shape [B, N, 3], got {tuple(t.shape)}")
+        if t.dtype != torch.float32:
+            raise TypeError(f"{name} must be float32 (my_lib.cpp:50-51 reads float), got {t.dtype}")
+        if not t.is_cuda:
+            raise RuntimeError(
+                f"{name} is on {t.device}: pointcloudregistration_b200 is the B200 build of nnd and has no CPU path")
+    if xyz1.size(0) != xyz2.size(0):
+        raise ValueError(f"batch sizes differ: {xyz1.size(0)} vs {xyz2.size(0)}")
+    if xyz1.device != xyz2.device:
+        raise RuntimeError(f"xyz1 is on {xyz1.device} but xyz2 is on {xyz2.device}")
+
+
+def _stream_ptr(device: torch.device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _workspace(nbytes: int, device: torch.device) -> torch.Tensor:
+    # torch's caching allocator hands out >=512-byte aligned blocks
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+def nnd_forward_raw(xyz1: torch.Tensor, xyz2: torch.Tensor):
+    """dist1[B,N], dist2[B,M] float32 and idx1[B,N], idx2[B,M] int32; no autograd."""
+    _check_clouds(xyz1, xyz2)
+    lib = _cabi.load()
+    xyz1 = xyz1.contiguous()
+    xyz2 = xyz2.contiguous()
+    b, n, _ = xyz1.shape
+    m = xyz2.size(1)
+    dev = xyz1.device
+    dist1 = torch.empty(b, n, dtype=torch.float32, device=dev)
+    dist2 = torch.empty(b, m, dtype=torch.float32, device=dev)
+    idx1 = torch.empty(b, n, dtype=torch.int32, device=dev)
+    idx2 = torch.empty(b, m, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        nbytes = lib.nnd_workspace_bytes(b, n, m)
+        ws = _workspace(nbytes, dev)
+        rc = lib.nnd_forward_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), b, n, m, dist1.data_ptr(), dist2.data_ptr(),
+                                      idx1.data_ptr(), idx2.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+    _cabi.check(rc, "nnd_forward_cuda_f32")
+    return dist1, dist2, idx1, idx2
+
+
+def nnd_query_raw(query: torch.Tensor, target: torch.Tensor):
+    """One direction: for every query point its nearest target. dist[B,Nq] f32, idx[B,Nq] int32."""
+    _check_clouds(query, target)
+    lib = _cabi.load()
+    query = query.contiguous()
+    target = target.contiguous()
+    b, nq, _ = query.shape
+    nt = target.size(1)
+    dev = query.device
+    dist = torch.empty(b, nq, dtype=torch.float32, device=dev)
+    idx = torch.empty(b, nq, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        ws = _workspace(lib.nnd_query_workspace_bytes(b, nq, nt), dev)
+        rc = lib.nnd_query_cuda_f32(query.data_ptr(), target.data_ptr(), b, nq, nt, dist.data_ptr(), idx.data_ptr(),
+                                    ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+    _cabi.check(rc, "nnd_query_cuda_f32")
+    return dist, idx
+
+
+def nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2):
+    """gradxyz1[B,N,3], gradxyz2[B,M,3] (my_lib.cpp:64-133 semantics, both always produced)."""
+    _check_clouds(xyz1, xyz2)
+    lib = _cabi.load()
+    xyz1 = xyz1.contiguous()
+    xyz2 = xyz2.contiguous()
+    b, n, _ = xyz1.shape
+    m = xyz2.size(1)
+    dev = xyz1.device
+    graddist1 = graddist1.to(device=dev, dtype=torch.float32).contiguous()  # __init__.py:40-41
+    graddist2 = graddist2.to(device=dev, dtype=torch.float32).contiguous()
+    if graddist1.shape != (b, n) or graddist2.shape != (b, m):
+        raise ValueError("graddist shapes must be [B,N] and [B,M]")
+    if idx1.dtype != torch.int32 or idx2.dtype != torch.int32:
+        raise TypeError("idx tensors must be int32 (__init__.py:19-20)")
+    idx1 = idx1.contiguous()
+    idx2 = idx2.contiguous()
+    gradxyz1 = torch.empty_like(xyz1)
+    gradxyz2 = torch.empty_like(xyz2)
+    with torch.cuda.device(dev):
+        rc = lib.nnd_backward_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), graddist1.data_ptr(), graddist2.data_ptr(),
+                                       idx1.data_ptr(), idx2.data_ptr(), b, n, m, gradxyz1.data_ptr(),
+                                       gradxyz2.data_ptr(), _stream_ptr(dev))
+    _cabi.check(rc, "nnd_backward_cuda_f32")
+    return gradxyz1, gradxyz2
+
+
+class NNDFunction(Function):
+    """torch_nndistance.NNDFunction (reference __init__.py:10-57)."""
+
+    @staticmethod
+    def forward(ctx, xyz1, xyz2):
+        dist1, dist2, idx1, idx2 = nnd_forward_raw(xyz1, xyz2)
+        ctx.save_for_backward(xyz1, xyz2, dist1, dist2, idx1, idx2)  # __init__.py:34
+        return dist1, dist2
+
+    @staticmethod
+    def backward(ctx, graddist1, graddist2):
+        xyz1, xyz2, dist1, dist2, idx1, idx2 = ctx.saved_tensors
+        return nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2)  # __init__.py:57
+
+
+class _NNDWithIdxFunction(Function):
+    @staticmethod
+    def forward(ctx, xyz1, xyz2):
+        dist1, dist2, idx1, idx2 = nnd_forward_raw(xyz1, xyz2)
+        ctx.save_for_backward(xyz1, xyz2, idx1, idx2)
+        ctx.mark_non_differentiable(idx1, idx2)
+        return dist1, dist2, idx1, idx2
+
+    @staticmethod
+    def backward(ctx, graddist1, graddist2, _gi1, _gi2):
+        xyz1, xyz2, idx1, idx2 = ctx.saved_tensors
+        return nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2)
+
+
+def nnd(xyz1, xyz2):
+    """dist1, dist2 = nnd(xyz1[B,N,3], xyz2[B,M,3]) -- squared L2 to the nearest neighbour, both ways
+    (reference __init__.py:60-61)."""
+    return NNDFunction.apply(xyz1, xyz2)
+
+
+def nnd_with_idx(xyz1, xyz2):
+    """dist1, dist2, idx1, idx2 -- the same op with the int32 neighbour indices exposed (non-differentiable)."""
+    return _NNDWithIdxFunction.apply(xyz1, xyz2)
+
+
+class NNDModule(torch.nn.Module):
+    """Legacy module name the reference smoke script still mentions (test.py:5-6)."""
+
+    def forward(self, xyz1, xyz2):
+        return nnd(xyz1, xyz2)

@@ -1,0 +1,76 @@
+"""CPU tests: libnnd_b200.so builds for sm_100a, loads, and exports every symbol include/nnd_b200.h
+declares.  No compute calls (there is no GPU here)."""
+import ctypes
+import re
+import subprocess
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+HEADER = ROOT / "include" / "nnd_b200.h"
+
+
+def declared_symbols():
+    text = re.sub(r"/\*.*?\*/", "", HEADER.read_text(), flags=re.S)
+    return sorted(set(re.findall(r"\b(nnd_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_declares_the_expected_entry_points():
+    syms = declared_symbols()
+    for s in ("nnd_forward_cuda_f32", "nnd_backward_cuda_f32", "nnd_query_cuda_f32", "nnd_backward_term_cuda_f32",
+              "nnd_workspace_bytes", "nnd_version"):
+        assert s in syms
+
+
+def test_library_loads_and_exports_every_declared_symbol(cuda_lib):
+    from pointcloudregistration_b200 import _cabi
+
+    raw = ctypes.CDLL(str(_cabi.LIB_PATH))
+    for s in declared_symbols():
+        assert hasattr(raw, s), f"{s} declared in include/nnd_b200.h but not exported"
+    assert set(_cabi.SIGNATURES) == set(declared_symbols()), "ctypes signature table out of sync with the header"
+
+
+def test_version_and_error_strings(cuda_lib):
+    assert b"sm_100a" in cuda_lib.nnd_version()
+    assert cuda_lib.nnd_error_string(0) == b"success"
+    assert b"workspace" in cuda_lib.nnd_error_string(10002)
+
+
+def test_workspace_size_formula(cuda_lib):
+    # SoA copies (12 B/point, padded to 512-point tiles) + 8 B/point keys for both clouds
+    w = cuda_lib.nnd_workspace_bytes(1, 1_000_000, 1_000_000)
+    assert 2 * 1_000_000 * 20 <= w <= 2 * 1_000_000 * 20 + 64 * 1024
+    assert cuda_lib.nnd_workspace_bytes(0, 10, 10) == 256
+    assert cuda_lib.nnd_query_workspace_bytes(2, 512, 512) == 2 * (2 * 512 * 12) + 2 * 512 * 8
+
+
+def test_argument_validation_needs_no_gpu(cuda_lib):
+    # negative sizes are rejected before any CUDA call
+    assert cuda_lib.nnd_forward_cuda_f32(None, None, -1, 1, 1, None, None, None, None, None, 0, None) == 10001
+    assert cuda_lib.nnd_backward_cuda_f32(None, None, None, None, None, None, 1, -5, 1, None, None, None) == 10001
+    # b == 0: nothing to do, success without touching the device
+    assert cuda_lib.nnd_forward_cuda_f32(None, None, 0, 4, 4, None, None, None, None, None, 0, None) == 0
+
+
+def test_forward_kernel_sass_is_bit_exact_form():
+    """The scan kernel must not contain a fused multiply-add of a real product: no scalar FFMA, and
+    exactly 2 FFMA2 (the run-time 1.0 adds) per 3 FMUL2 / 3 FADD2 (grep the cubin)."""
+    from pointcloudregistration_b200 import _cabi
+
+    try:
+        out = subprocess.run(["cuobjdump", "-sass", str(_cabi.LIB_PATH)], capture_output=True, text=True, check=True)
+    except (FileNotFoundError, subprocess.CalledProcessError):
+        pytest.skip("cuobjdump not available")
+    kernels = re.split(r"Function : ", out.stdout)
+    scan = [k for k in kernels if "nnd_scan_kernel" in k.split("\n", 1)[0]]
+    assert scan, "nnd_scan_kernel not found in the cubin"
+    for k in scan:
+        ops = re.findall(r"^\s+/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", k, flags=re.M)
+        n = {name: sum(1 for o in ops if o.split(".")[0] == name) for name in ("FFMA", "FMUL2", "FADD2", "FFMA2", "FMNMX3")}
+        assert n["FFMA"] == 0, f"scalar FFMA in the forward kernel: {n}"
+        assert n["FMUL2"] > 0 and n["FMUL2"] == n["FADD2"], n
+        assert 3 * n["FFMA2"] == 2 * n["FMUL2"], f"FFMA2:FMUL2 must be 2:3 (adds only), got {n}"
+        assert n["FMNMX3"] > 0
+    assert "UBLKCP" in out.stdout, "1-D TMA bulk copy (UBLKCP) missing from the forward kernel"

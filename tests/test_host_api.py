@@ -1,0 +1,63 @@
+"""CPU tests of the host-side mirror of the reference interface (names, validation, error behaviour)."""
+import pytest
+import torch
+
+
+def test_drop_in_names_exist():
+    import torch_nndistance as NND
+    import torch_nndistance_aten as my_lib
+
+    assert NND.__version__ == "1.0.0"  # reference torch_nndistance/__init__.py:1
+    assert callable(NND.nnd) and issubclass(NND.NNDFunction, torch.autograd.Function)
+    assert hasattr(NND.NNDFunction, "forward") and hasattr(NND.NNDFunction, "backward")
+    assert isinstance(NND.NNDModule(), torch.nn.Module)
+    for name in ("nnd_forward_cuda", "nnd_backward_cuda", "nnd_forward", "nnd_backward"):
+        assert callable(getattr(my_lib, name))  # my_lib_cuda.cpp:74-77, my_lib.cpp:135-138
+
+
+def test_cpu_tensors_are_rejected_not_silently_computed():
+    import torch_nndistance as NND
+    import torch_nndistance_aten as my_lib
+
+    a, b = torch.rand(1, 8, 3), torch.rand(1, 9, 3)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        NND.nnd(a, b)
+    with pytest.raises(RuntimeError, match="CUDA tensor"):
+        my_lib.nnd_forward_cuda(a, b, torch.zeros(1, 8), torch.zeros(1, 9), torch.zeros(1, 8, dtype=torch.int32),
+                                torch.zeros(1, 9, dtype=torch.int32))
+    with pytest.raises(RuntimeError, match="B200 build"):
+        my_lib.nnd_forward(a, b, None, None, None, None)
+
+
+@pytest.mark.parametrize("bad, exc", [
+    (lambda: (torch.rand(8, 3), torch.rand(1, 8, 3)), ValueError),
+    (lambda: (torch.rand(1, 8, 4), torch.rand(1, 8, 3)), ValueError),
+    (lambda: (torch.rand(1, 8, 3).double(), torch.rand(1, 8, 3)), TypeError),
+    (lambda: ([[0.0, 0.0, 0.0]], torch.rand(1, 8, 3)), TypeError),
+])
+def test_shape_and_dtype_validation(bad, exc):
+    from pointcloudregistration_b200.functional import _check_clouds
+
+    with pytest.raises(exc):
+        _check_clouds(*bad())
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    from pointcloudregistration_b200 import _cabi
+
+    monkeypatch.setattr(_cabi, "_lib", None)
+    monkeypatch.setattr(_cabi, "LIB_PATH", tmp_path / "libnnd_b200.so")
+    with pytest.raises(_cabi.NNDLibraryError, match="no CPU fallback"):
+        _cabi.load()
+
+
+def test_product_never_imports_the_oracle():
+    import pathlib
+    import re
+
+    root = pathlib.Path(__file__).resolve().parent.parent
+    files = list((root / "pointcloudregistration_b200").rglob("*.py")) + list((root / "torch_nndistance").rglob("*.py"))
+    files.append(root / "torch_nndistance_aten.py")
+    for f in files:
+        src = f.read_text()
+        assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f"{f} imports the oracle"

@@ -1,0 +1,113 @@
+"""CPU tests of the multi-GPU host logic: world_size-2 (and 3) `gloo` process groups with the oracle
+injected as the per-rank engine.  Checks: forward bit-identical to the unsharded oracle for any G,
+gradients within 1e-5, broadcast from src, uneven shards."""
+import os
+import socket
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+
+class OracleCompute:
+    """Test-only engine: same interface as sharded.CudaCompute, backed by oracle/ (CPU)."""
+
+    @staticmethod
+    def query(q, t):
+        import oracle
+
+        d, i = oracle.query(q.numpy(), t.numpy())
+        return torch.from_numpy(d), torch.from_numpy(i)
+
+    @staticmethod
+    def backward_term(q, t, gd, idx, grad_q, grad_t):
+        qn, tn, g, ix = q.numpy(), t.numpy(), gd.numpy(), idx.numpy().astype(np.int64)
+        for b in range(qn.shape[0]):
+            tt = (g[b] * np.float32(2))[:, None] * (qn[b] - tn[b][ix[b]])
+            grad_q[b] += torch.from_numpy(tt)
+            np.subtract.at(grad_t[b].numpy(), ix[b], tt)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, b, n, m, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from pointcloudregistration_b200 import sharded, synthetic
+
+        x1, x2 = synthetic.make_pair("crosscopy", b, n, m, 60)
+        if rank != 0:  # only the source holds real data; the others receive it by broadcast
+            x1, x2 = torch.zeros_like(x1), torch.zeros_like(x2)
+        a = x1.clone().requires_grad_(True)
+        c = x2.clone().requires_grad_(True)
+        with torch.no_grad():
+            dist.broadcast(a, 0)
+            dist.broadcast(c, 0)
+        d1, d2, i1, i2 = sharded.nnd_sharded_with_idx(a, c, src=None, compute=OracleCompute)
+        gd1, gd2 = synthetic.grad_pair(b, n, m, 60)
+        ((d1 * gd1).sum() + (d2 * gd2).sum()).backward()
+        torch.save(dict(d1=d1.detach(), d2=d2.detach(), i1=i1, i2=i2, g1=a.grad, g2=c.grad), f"{out}/r{rank}.pt")
+        # shard-only mode + explicit broadcast from src
+        y1, y2 = synthetic.make_pair("crosscopy", b, n, m, 60)
+        if rank != 0:
+            y1, y2 = torch.zeros_like(y1), torch.zeros_like(y2)
+        s1, s2, j1, j2, info = sharded.sharded_forward(y1, y2, src=0, gather=False, compute=OracleCompute)
+        assert s1.shape == (b, info.hi1 - info.lo1) and s2.shape == (b, info.hi2 - info.lo2)
+        assert torch.equal(s1, d1.detach()[:, info.lo1:info.hi1]) and torch.equal(j2, i2[:, info.lo2:info.hi2])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,b,n,m", [(2, 1, 301, 200), (2, 3, 64, 129), (3, 1, 100, 101)])
+def test_sharded_matches_unsharded(world, b, n, m, tmp_path):
+    import oracle
+    from _util import assert_forward_exact, assert_grad_close
+    from pointcloudregistration_b200 import synthetic
+
+    mp.spawn(_worker, args=(world, _free_port(), b, n, m, str(tmp_path)), nprocs=world, join=True)
+    x1, x2 = synthetic.make_pair("crosscopy", b, n, m, 60)
+    gd1, gd2 = synthetic.grad_pair(b, n, m, 60)
+    want = oracle.forward(x1.numpy(), x2.numpy())
+    wg = oracle.backward(x1.numpy(), x2.numpy(), gd1.numpy(), gd2.numpy(), want[2], want[3])
+    for r in range(world):
+        z = torch.load(f"{tmp_path}/r{r}.pt")
+        assert_forward_exact(tuple(z[k].numpy() for k in ("d1", "d2", "i1", "i2")), want, what=f"rank {r}: ")
+        assert_grad_close((z["g1"].numpy(), z["g2"].numpy()), wg, what=f"rank {r}: ")
+
+
+def test_shard_ranges_cover_and_balance():
+    from pointcloudregistration_b200.sharded import shard_range
+
+    for n in (0, 1, 7, 8, 1_000_000, 1_000_003):
+        for w in (1, 2, 3, 4, 8):
+            r = [shard_range(n, w, k) for k in range(w)]
+            assert r[0][0] == 0 and r[-1][1] == n
+            assert all(r[k][1] == r[k + 1][0] for k in range(w - 1))
+            sizes = [hi - lo for lo, hi in r]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_single_process_without_process_group():
+    from pointcloudregistration_b200 import sharded, synthetic
+    import oracle
+
+    x1, x2 = synthetic.make_pair("uniform", 2, 50, 60, 61)
+    d1, d2, i1, i2, info = sharded.sharded_forward(x1, x2, compute=OracleCompute)
+    assert info.world == 1
+    want = oracle.forward(x1.numpy(), x2.numpy())
+    assert np.array_equal(d1.numpy(), want[0]) and np.array_equal(i2.numpy(), want[3])
