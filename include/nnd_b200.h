@@ -61,6 +61,15 @@ int nnd_forward_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int
                          float *dist1, float *dist2, int32_t *idx1, int32_t *idx2,
                          void *workspace, size_t workspace_bytes, void *stream);
 
+/* Measurement aid for bench.py's roofline block.  While enabled (per calling thread), every forward /
+ * query call also records CUDA events on its stream around each of its three kernels (no
+ * synchronisation, up to 64 calls are remembered).  nnd_profile_collect waits for those events and
+ * returns the summed kernel durations in milliseconds since the last collect:
+ * kernel_ms[0] = prepare (AoS->SoA), [1] = scan (the dominant kernel), [2] = finalize (key unpack),
+ * and the number of calls they cover. */
+int nnd_profile_enable(int on);
+int nnd_profile_collect(float *kernel_ms, int *calls);
+
 /* One direction only (the unit the query-sharded multi-GPU path calls):
  * for every query point its nearest target point. */
 int nnd_query_cuda_f32(const float *query, const float *target, int b, int nq, int nt,

@@ -10,7 +10,10 @@ import ctypes
 from ctypes import c_char_p, c_int, c_size_t, c_void_p
 from pathlib import Path
 
-LIB_PATH = Path(__file__).resolve().parent / "libnnd_b200.so"
+import os
+
+# NND_B200_LIB: developer override to time an experimental build of the same ABI (tools/variants.sh)
+LIB_PATH = Path(os.environ.get("NND_B200_LIB") or Path(__file__).resolve().parent / "libnnd_b200.so")
 
 #: every symbol include/nnd_b200.h declares -> (restype, argtypes)
 SIGNATURES = {
@@ -20,6 +23,8 @@ SIGNATURES = {
     "nnd_query_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "nnd_forward_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                       c_void_p, c_void_p, c_size_t, c_void_p]),
+    "nnd_profile_enable": (c_int, [c_int]),
+    "nnd_profile_collect": (c_int, [c_void_p, c_void_p]),
     "nnd_query_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                     c_size_t, c_void_p]),
     "nnd_backward_cuda_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,

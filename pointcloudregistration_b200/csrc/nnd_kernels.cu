@@ -13,8 +13,9 @@
 //   * nnd_prepare_kernel rewrites each [n,3] cloud once into structure-of-arrays
 //     tiles  x[TT] | y[TT] | z[TT]  (last tile padded by repeating the last point:
 //     a duplicate at a higher index can never win the lowest-index tie-break).
-//   * nnd_scan_kernel: persistent CTAs, work item = (direction, batch, query block,
-//     target split).  Target tiles arrive in shared memory by 1-D TMA bulk copies
+//   * nnd_scan_kernel: persistent CTAs; the work is the linear list of (direction, batch,
+//     query block, target tile) units and every CTA owns an equal contiguous share of it
+//     (balanced to one tile).  Target tiles arrive in shared memory by 1-D TMA bulk copies
 //     (cp.async.bulk + mbarrier, multi-stage ring).  Each thread keeps QPT queries in
 //     registers, duplicated into both halves of a 64-bit register pair and negated, so
 //     one packed instruction evaluates two targets:
@@ -22,12 +23,13 @@
 //         (fma(a,1,b) == fl(a+b); ptxas would contract mul.rn.f32x2 + add.rn.f32x2 into
 //          one FFMA2 and change the rounding, the run-time 1.0 makes that impossible)
 //     = 8 packed instructions per 2 pairs, each product and sum separately rounded.
-//   * running minimum with one 3-input FMNMX per 2 pairs; the index is recovered
-//     lazily: after each chunk of C targets the thread compares best against its value
-//     before the chunk and only then rescans the chunk for the lowest k with d == best.
-//   * partial results of target splits merge through atomicMin on a packed
-//     (dist_bits << 32 | idx) key: d >= +0 so uint order == float order, and the
-//     smaller idx wins exact ties.  nnd_finalize_kernel unpacks keys to dist/idx.
+//   * minimum with one 3-input FMNMX per 2 pairs; the index is recovered lazily: per chunk
+//     of C targets the thread keeps only the chunk minimum and, when it beats the running
+//     best (strict <, ascending order), remembers WHICH chunk.
+//   * partial results of different CTAs merge through atomicMin on a packed
+//     (dist_bits << 32 | chunk_base) key: d >= +0 so uint order == float order, and the
+//     earlier chunk wins exact ties.  nnd_finalize_kernel re-evaluates that single chunk per
+//     query (same instruction sequence => same bits) and takes the lowest k with d == dist.
 //
 // Backward: nnd_grad_kernel, one thread per (term, batch, row); warp-aggregated
 // (match.any on the neighbour index) fp32 atomics into zero-initialised grads.
@@ -38,6 +40,9 @@
 
 #include "nnd_b200.h"
 
+#ifndef NND_MIN_VARIANT
+#define NND_MIN_VARIANT 0
+#endif
 #define NND_VERSION_STRING "nnd_b200 0.1.0 sm_100a"
 
 namespace {
@@ -71,6 +76,15 @@ __device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
 __device__ __forceinline__ float fmin3(float a, float b, float c) {
   float r;
   asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+
+// min for operands that are both >= +0: |min(|a|,|b|)| with sign = sign(a)^sign(b) = +.  Same value as
+// min.f32 on such inputs, but a different opcode flavour, which keeps ptxas from merging two 2-input
+// FMNMX into one 3-input FMNMX3 (measured slower inside a saturated packed-FP32 stream).
+__device__ __forceinline__ float fmin_xs(float a, float b) {
+  float r;
+  asm("min.xorsign.abs.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
   return r;
 }
 
@@ -123,18 +137,16 @@ __device__ __forceinline__ void tma_load_1d(void* smem_dst, const void* gmem_src
 struct ScanDir {
   const float* qsoa;         // [b][qtiles][3][TT]   queries of this direction
   const float* tsoa;         // [b][ttiles][3][TT]   targets of this direction
-  unsigned long long* keys;  // [b][nq]  packed (dist_bits << 32 | idx), pre-set to ~0
+  unsigned long long* keys;  // [b][nq]  packed (dist_bits << 32 | chunk_base), pre-set to ~0
   int nq, nt;
   int qtiles, ttiles;
-  int qblocks;          // ceil(nq / QB)
-  int splits;           // target splits per query block
-  int tiles_per_split;  // ceil(ttiles / splits)
-  int items;            // b * qblocks * splits
+  int qblocks;      // ceil(nq / QB)
+  long long units;  // b * qblocks * ttiles   (one unit = one query block x one target tile)
 };
 struct ScanParams {
   ScanDir d[2];
   int ndir;
-  int total_items;
+  long long total_units;
   float one;  // 1.0f, deliberately opaque to the compiler (see header comment)
 };
 
@@ -151,14 +163,18 @@ struct PrepParams {
 };
 
 struct FinDir {
-  const unsigned long long* keys;
+  const unsigned long long* keys;  // [b][nq]
+  const float* q;                  // [b][nq][3] original query cloud (AoS)
+  const float* tsoa;               // [b][ttiles][3][TT]
   float* dist;
   int32_t* idx;
+  int nq, ttiles;
   long long count;  // b * nq
 };
 struct FinParams {
   FinDir d[2];
   int ndir;
+  float one;
 };
 
 // ----------------------------------------------------------------------------------
@@ -186,16 +202,45 @@ __global__ void __launch_bounds__(256) nnd_prepare_kernel(PrepParams p) {
 }
 
 // ----------------------------------------------------------------------------------
-// finalize: packed keys -> dist (high word, float bits) + idx (low word)
+// finalize: key = (dist_bits << 32 | first index of the C-target chunk that attains the minimum).
+// One thread per query re-evaluates that one chunk with the same instruction sequence as the scan
+// (bit-identical distances) and takes the lowest k with d == dist  (my_lib.cpp:16: first wins).
 // ----------------------------------------------------------------------------------
+template <int TT, int C>
 __global__ void __launch_bounds__(256) nnd_finalize_kernel(FinParams p) {
   const long long stride = (long long)gridDim.x * blockDim.x;
+  const uint64_t one = pk2(p.one, p.one);
   for (int di = 0; di < p.ndir; ++di) {
     const FinDir d = p.d[di];
     for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < d.count; g += stride) {
-      const unsigned long long k = d.keys[g];
-      d.dist[g] = __uint_as_float((unsigned)(k >> 32));
-      d.idx[g] = (int32_t)(unsigned)(k & 0xffffffffull);
+      const unsigned long long key = d.keys[g];
+      const float bq = __uint_as_float((unsigned)(key >> 32));
+      const int base = (int)(unsigned)(key & 0xffffffffull);
+      const long long batch = g / d.nq;
+      const float* qp = d.q + g * 3;
+      const float x = -qp[0], y = -qp[1], z = -qp[2];
+      const uint64_t nqx = pk2(x, x), nqy = pk2(y, y), nqz = pk2(z, z);
+      const int tile = base / TT, off = base - tile * TT;
+      const float* sx = d.tsoa + ((batch * d.ttiles + tile) * 3) * (long long)TT + off;
+      const ulonglong2* cx = reinterpret_cast<const ulonglong2*>(sx);
+      const ulonglong2* cy = reinterpret_cast<const ulonglong2*>(sx + TT);
+      const ulonglong2* cz = reinterpret_cast<const ulonglong2*>(sx + 2 * TT);
+      int found = 0;
+#pragma unroll
+      for (int s4 = C / 4 - 1; s4 >= 0; --s4) {  // descending: the last hit is the lowest k
+        const ulonglong2 X = __ldg(cx + s4), Y = __ldg(cy + s4), Z = __ldg(cz + s4);
+        const uint64_t d0 = sqdist2(X.x, Y.x, Z.x, nqx, nqy, nqz, one);
+        const uint64_t d1 = sqdist2(X.y, Y.y, Z.y, nqx, nqy, nqz, one);
+        float a0, a1, b0, b1;
+        upk2(d0, a0, a1);
+        upk2(d1, b0, b1);
+        if (b1 == bq) found = 4 * s4 + 3;
+        if (b0 == bq) found = 4 * s4 + 2;
+        if (a1 == bq) found = 4 * s4 + 1;
+        if (a0 == bq) found = 4 * s4;
+      }
+      d.dist[g] = bq;
+      d.idx[g] = base + found;
     }
   }
 }
@@ -203,44 +248,24 @@ __global__ void __launch_bounds__(256) nnd_finalize_kernel(FinParams p) {
 // ----------------------------------------------------------------------------------
 // scan: the hot kernel
 // ----------------------------------------------------------------------------------
-struct ItemCoords {
-  int dir, batch, qblock, tile_begin, tile_end;
+// Work is the linear sequence of units (direction, batch, query block, target tile), tile fastest.
+// CTA c owns the contiguous range [U*c/G, U*(c+1)/G): perfectly balanced to one tile, and the tile
+// stream of a CTA is contiguous in memory within a query block.  A CTA's range may start or end in the
+// middle of a query block's tile list; partial results merge through atomicMin on the packed keys.
+struct UnitCoords {
+  int dir, batch, qblock, tile;
 };
-__device__ __forceinline__ ItemCoords decode_item(const ScanParams& p, int item) {
-  ItemCoords c;
-  c.dir = (p.ndir > 1 && item >= p.d[0].items) ? 1 : 0;
+__device__ __forceinline__ UnitCoords decode_unit(const ScanParams& p, long long u) {
+  UnitCoords c;
+  c.dir = (p.ndir > 1 && u >= p.d[0].units) ? 1 : 0;
   const ScanDir& d = p.d[c.dir];
-  int local = item - (c.dir ? p.d[0].items : 0);
-  const int split = local % d.splits;
-  local /= d.splits;
-  c.qblock = local % d.qblocks;
-  c.batch = local / d.qblocks;
-  c.tile_begin = split * d.tiles_per_split;
-  c.tile_end = min(c.tile_begin + d.tiles_per_split, d.ttiles);
+  if (c.dir) u -= p.d[0].units;
+  const long long qb = u / d.ttiles;
+  c.tile = (int)(u - qb * d.ttiles);
+  c.batch = (int)(qb / d.qblocks);
+  c.qblock = (int)(qb - (long long)c.batch * d.qblocks);
   return c;
 }
-
-// Producer side of the tile ring: walks the same (item, tile) sequence as the consumers.
-template <int TT>
-struct TileCursor {
-  int item, tile, tile_end;
-  const float* base;  // tsoa + batch offset of the current item
-  __device__ __forceinline__ void open(const ScanParams& p, int it) {
-    item = it;
-    if (item < p.total_items) {
-      const ItemCoords c = decode_item(p, item);
-      const ScanDir& d = p.d[c.dir];
-      tile = c.tile_begin;
-      tile_end = c.tile_end;
-      base = d.tsoa + (long long)c.batch * d.ttiles * (3 * TT);
-    }
-  }
-  __device__ __forceinline__ bool valid(const ScanParams& p) const { return item < p.total_items; }
-  __device__ __forceinline__ const float* src() const { return base + (long long)tile * (3 * TT); }
-  __device__ __forceinline__ void advance(const ScanParams& p, int grid) {
-    if (++tile >= tile_end) open(p, item + grid);
-  }
-};
 
 template <int THREADS, int QPT, int TT, int C, int STAGES, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_constant__ ScanParams p) {
@@ -251,6 +276,9 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
   __shared__ __align__(8) uint64_t full[STAGES];
 
   const int tid = threadIdx.x;
+  const long long u_begin = p.total_units * blockIdx.x / gridDim.x;
+  const long long u_end = p.total_units * (blockIdx.x + 1) / gridDim.x;
+
   if (tid == 0) {
 #pragma unroll
     for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
@@ -258,34 +286,40 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
   }
   __syncthreads();
 
-  TileCursor<TT> prod;
+  // producer (thread 0): unit `pu` is the next tile to fetch
+  long long pu = u_begin;
+  auto produce = [&](int stage) {
+    const UnitCoords c = decode_unit(p, pu);
+    const ScanDir& d = p.d[c.dir];
+    const float* src = d.tsoa + ((long long)c.batch * d.ttiles + c.tile) * (3 * TT);
+    mbar_expect_tx(&full[stage], TILE_BYTES);
+    tma_load_1d(&tiles[stage][0], src, TILE_BYTES, &full[stage]);
+    ++pu;
+  };
   if (tid == 0) {
-    prod.open(p, blockIdx.x);
 #pragma unroll
-    for (int s = 0; s < STAGES; ++s) {
-      if (prod.valid(p)) {
-        mbar_expect_tx(&full[s], TILE_BYTES);
-        tma_load_1d(&tiles[s][0], prod.src(), TILE_BYTES, &full[s]);
-        prod.advance(p, gridDim.x);
-      }
-    }
+    for (int s = 0; s < STAGES; ++s)
+      if (pu < u_end) produce(s);
   }
 
   const uint64_t one = pk2(p.one, p.one);
   uint32_t cnt = 0;  // tiles consumed by this CTA so far
 
-  for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-    const ItemCoords ic = decode_item(p, item);
-    const ScanDir& d = p.d[ic.dir];
+  long long u = u_begin;
+  while (u < u_end) {
+    const UnitCoords uc = decode_unit(p, u);
+    const ScanDir& d = p.d[uc.dir];
+    const long long rest = (long long)d.ttiles - uc.tile;  // tiles left in this query block's list
+    const int seg_tiles = (int)(u_end - u < rest ? u_end - u : rest);
 
     // ---- queries -> registers (negated, duplicated in both halves)
     uint64_t nqx[QPT], nqy[QPT], nqz[QPT];
-    float best[QPT], prev[QPT];
-    int besti[QPT];
-    const float* qbase = d.qsoa + (long long)ic.batch * d.qtiles * (3 * TT);
+    float best[QPT];
+    int bchunk[QPT];  // first index of the first chunk that attains best
+    const float* qbase = d.qsoa + (long long)uc.batch * d.qtiles * (3 * TT);
 #pragma unroll
     for (int q = 0; q < QPT; ++q) {
-      int j = ic.qblock * QB + q * THREADS + tid;
+      int j = uc.qblock * QB + q * THREADS + tid;
       j = j < d.nq ? j : d.nq - 1;
       const int qt = j / TT, qo = j - qt * TT;
       const float* s = qbase + (long long)qt * (3 * TT) + qo;
@@ -294,11 +328,10 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
       nqy[q] = pk2(y, y);
       nqz[q] = pk2(z, z);
       best[q] = __int_as_float(0x7f800000);  // +inf: an all-inf row keeps idx 0 like the reference
-      prev[q] = best[q];
-      besti[q] = 0;
+      bchunk[q] = 0;
     }
 
-    for (int tile = ic.tile_begin; tile < ic.tile_end; ++tile) {
+    for (int tile = uc.tile; tile < uc.tile + seg_tiles; ++tile) {
       const int stage = cnt % STAGES;
       mbar_wait(&full[stage], (cnt / STAGES) & 1);
       const float* sx = &tiles[stage][0];
@@ -311,6 +344,9 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
         const ulonglong2* cx = reinterpret_cast<const ulonglong2*>(sx + ch * C);
         const ulonglong2* cy = reinterpret_cast<const ulonglong2*>(sy + ch * C);
         const ulonglong2* cz = reinterpret_cast<const ulonglong2*>(sz + ch * C);
+        float cm[QPT];  // minimum over this chunk only
+#pragma unroll
+        for (int q = 0; q < QPT; ++q) cm[q] = __int_as_float(0x7f800000);
 #pragma unroll
         for (int s4 = 0; s4 < C / 4; ++s4) {
           const ulonglong2 X = cx[s4], Y = cy[s4], Z = cz[s4];  // 3 x LDS.128 broadcast = 4 targets
@@ -321,58 +357,39 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
             float a0, a1, b0, b1;
             upk2(d0, a0, a1);
             upk2(d1, b0, b1);
-            best[q] = fmin3(best[q], fmin3(a0, a1, b0), b1);
+            cm[q] = fmin3(cm[q], a0, a1);
+            cm[q] = fmin3(cm[q], b0, b1);
           }
         }
-        // ---- lazy index recovery (rare after the first few chunks)
-        bool hit = false;
+        // strict < in ascending chunk order: the first chunk that attains the minimum is remembered
+        const int cbase = tile * TT + ch * C;
 #pragma unroll
-        for (int q = 0; q < QPT; ++q) hit |= best[q] < prev[q];
-        if (hit) {
-          const uint64_t* rx = reinterpret_cast<const uint64_t*>(sx + ch * C);
-          const uint64_t* ry = reinterpret_cast<const uint64_t*>(sy + ch * C);
-          const uint64_t* rz = reinterpret_cast<const uint64_t*>(sz + ch * C);
-#pragma unroll
-          for (int q = 0; q < QPT; ++q) {
-            if (best[q] < prev[q]) {
-              const float bq = best[q];
-              int found = 0;
-#pragma unroll 1
-              for (int k2 = C / 2 - 1; k2 >= 0; --k2) {  // descending: the last hit is the lowest k
-                const uint64_t dd = sqdist2(rx[k2], ry[k2], rz[k2], nqx[q], nqy[q], nqz[q], one);
-                float lo, hi;
-                upk2(dd, lo, hi);
-                if (hi == bq) found = 2 * k2 + 1;
-                if (lo == bq) found = 2 * k2;
-              }
-              besti[q] = tile * TT + ch * C + found;
-              prev[q] = bq;
-            }
-          }
+        for (int q = 0; q < QPT; ++q) {
+          if (cm[q] < best[q]) bchunk[q] = cbase;
+          best[q] = fminf(best[q], cm[q]);
         }
       }
 
       __syncthreads();  // every thread is done reading this stage
-      if (tid == 0 && prod.valid(p)) {
+      if (tid == 0 && pu < u_end) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        mbar_expect_tx(&full[stage], TILE_BYTES);
-        tma_load_1d(&tiles[stage][0], prod.src(), TILE_BYTES, &full[stage]);
-        prod.advance(p, gridDim.x);
+        produce(stage);
       }
       ++cnt;
     }
 
-    // ---- merge this split's result: smaller dist wins, then smaller idx
-    unsigned long long* keys = d.keys + (long long)ic.batch * d.nq;
+    // ---- merge this segment's result: smaller dist wins, then the earlier chunk
+    unsigned long long* keys = d.keys + (long long)uc.batch * d.nq;
 #pragma unroll
     for (int q = 0; q < QPT; ++q) {
-      const int j = ic.qblock * QB + q * THREADS + tid;
+      const int j = uc.qblock * QB + q * THREADS + tid;
       if (j < d.nq) {
         const unsigned long long key =
-            ((unsigned long long)__float_as_uint(best[q]) << 32) | (unsigned long long)(unsigned)besti[q];
+            ((unsigned long long)__float_as_uint(best[q]) << 32) | (unsigned long long)(unsigned)bchunk[q];
         atomicMin(keys + j, key);
       }
     }
+    u += seg_tiles;
   }
 }
 
@@ -459,6 +476,15 @@ constexpr int kQB = kThreads * kQPT;
 
 thread_local int g_launches = 0;
 
+// optional per-kernel event timing of the forward (bench.py's roofline block)
+constexpr int kProfSlots = 64;
+struct Profiler {
+  bool enabled = false, created = false;
+  int used = 0;
+  cudaEvent_t ev[kProfSlots * 4];
+};
+thread_local Profiler g_prof;
+
 struct DeviceInfo {
   int sms = 0;
   int major = 0;
@@ -487,17 +513,11 @@ inline int tiles_of(int n) { return (n + kTT - 1) / kTT; }
 inline size_t soa_bytes(int b, int n) { return align_up((size_t)b * tiles_of(n) * 3 * kTT * sizeof(float), 256); }
 inline size_t key_bytes(int b, int n) { return align_up((size_t)b * n * sizeof(unsigned long long), 256); }
 
-void plan_dir(ScanDir& d, int b, int grid, int base_items_all) {
+void plan_dir(ScanDir& d, int b) {
   d.qtiles = tiles_of(d.nq);
   d.ttiles = tiles_of(d.nt);
   d.qblocks = (d.nq + kQB - 1) / kQB;
-  // enough items that static striding over the persistent grid balances to a few percent
-  long long want = ((long long)24 * grid + base_items_all - 1) / base_items_all;
-  int splits = (int)(want < 1 ? 1 : want);
-  if (splits > d.ttiles) splits = d.ttiles;
-  d.tiles_per_split = (d.ttiles + splits - 1) / splits;
-  d.splits = (d.ttiles + d.tiles_per_split - 1) / d.tiles_per_split;
-  d.items = b * d.qblocks * d.splits;
+  d.units = (long long)b * d.qblocks * d.ttiles;
 }
 
 int check_last(cudaError_t e) { return e == cudaSuccess ? 0 : (int)e; }
@@ -506,6 +526,8 @@ int check_last(cudaError_t e) { return e == cudaSuccess ? 0 : (int)e; }
 // dirs: (query cloud, nq, target cloud, nt, dist, idx); ndir == 2 means the two clouds swap roles.
 int forward_impl(const float* c1, int n1, const float* c2, int n2, int b, int ndir, float* dist1, int32_t* idx1,
                  float* dist2, int32_t* idx2, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  cudaEvent_t* ev = nullptr;
+  if (g_prof.enabled && g_prof.used < kProfSlots) ev = &g_prof.ev[4 * g_prof.used++];
   DeviceInfo di;
   int rc = device_info(&di);
   if (rc) return rc;
@@ -529,8 +551,10 @@ int forward_impl(const float* c1, int n1, const float* c2, int n2, int b, int nd
     const long long total = pp.c[0].padded_total > pp.c[1].padded_total ? pp.c[0].padded_total : pp.c[1].padded_total;
     long long blocks = (total + 255) / 256;
     if (blocks > (long long)di.sms * 16) blocks = (long long)di.sms * 16;
+    if (ev) cudaEventRecord(ev[0], st);
     nnd_prepare_kernel<kTT><<<(unsigned)blocks, 256, 0, st>>>(pp);
     ++g_launches;
+    if (ev) cudaEventRecord(ev[1], st);
   }
 
   const int grid_full = di.sms * kMinBlocks;
@@ -549,23 +573,25 @@ int forward_impl(const float* c1, int n1, const float* c2, int n2, int b, int nd
     sp.d[1].nq = n2;
     sp.d[1].nt = n1;
   }
-  int base_items = b * ((n1 + kQB - 1) / kQB) + (ndir == 2 ? b * ((n2 + kQB - 1) / kQB) : 0);
-  for (int i = 0; i < ndir; ++i) plan_dir(sp.d[i], b, grid_full, base_items);
-  sp.total_items = sp.d[0].items + (ndir == 2 ? sp.d[1].items : 0);
-  const int grid = sp.total_items < grid_full ? sp.total_items : grid_full;
+  for (int i = 0; i < ndir; ++i) plan_dir(sp.d[i], b);
+  sp.total_units = sp.d[0].units + (ndir == 2 ? sp.d[1].units : 0);
+  const int grid = sp.total_units < grid_full ? (int)sp.total_units : grid_full;
   nnd_scan_kernel<kThreads, kQPT, kTT, kChunk, kStages, kMinBlocks><<<grid, kThreads, 0, st>>>(sp);
   ++g_launches;
+  if (ev) cudaEventRecord(ev[2], st);
 
   FinParams fp{};
   fp.ndir = ndir;
-  fp.d[0] = FinDir{keys1, dist1, idx1, (long long)b * n1};
-  if (ndir == 2) fp.d[1] = FinDir{keys2, dist2, idx2, (long long)b * n2};
+  fp.one = 1.0f;
+  fp.d[0] = FinDir{keys1, c1, soa2, dist1, idx1, n1, tiles_of(n2), (long long)b * n1};
+  if (ndir == 2) fp.d[1] = FinDir{keys2, c2, soa1, dist2, idx2, n2, tiles_of(n1), (long long)b * n2};
   {
     const long long total = fp.d[0].count > fp.d[1].count ? fp.d[0].count : fp.d[1].count;
     long long blocks = (total + 255) / 256;
     if (blocks > (long long)di.sms * 16) blocks = (long long)di.sms * 16;
-    nnd_finalize_kernel<<<(unsigned)blocks, 256, 0, st>>>(fp);
+    nnd_finalize_kernel<kTT, kChunk><<<(unsigned)blocks, 256, 0, st>>>(fp);
     ++g_launches;
+    if (ev) cudaEventRecord(ev[3], st);
   }
   return check_last(cudaGetLastError());
 }
@@ -634,6 +660,38 @@ int nnd_forward_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int
   if (m == 0) return zero_outputs(dist1, idx1, (long long)b * n, st);
   if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2 || !workspace) return NND_EINVAL;
   return forward_impl(xyz1, n, xyz2, m, b, 2, dist1, idx1, dist2, idx2, workspace, workspace_bytes, st);
+}
+
+int nnd_profile_enable(int on) {
+  g_prof.enabled = on != 0;
+  g_prof.used = 0;
+  if (on && !g_prof.created) {
+    for (int i = 0; i < kProfSlots * 4; ++i) {
+      cudaError_t e = cudaEventCreate(&g_prof.ev[i]);
+      if (e != cudaSuccess) return (int)e;
+    }
+    g_prof.created = true;
+  }
+  return 0;
+}
+
+int nnd_profile_collect(float* kernel_ms, int* calls) {
+  if (!kernel_ms || !calls) return NND_EINVAL;
+  kernel_ms[0] = kernel_ms[1] = kernel_ms[2] = 0.f;
+  *calls = g_prof.used;
+  for (int c = 0; c < g_prof.used; ++c) {
+    cudaEvent_t* ev = &g_prof.ev[c * 4];
+    cudaError_t e = cudaEventSynchronize(ev[3]);
+    if (e != cudaSuccess) return (int)e;
+    for (int i = 0; i < 3; ++i) {
+      float ms = 0.f;
+      e = cudaEventElapsedTime(&ms, ev[i], ev[i + 1]);
+      if (e != cudaSuccess) return (int)e;
+      kernel_ms[i] += ms;
+    }
+  }
+  g_prof.used = 0;
+  return 0;
 }
 
 int nnd_query_cuda_f32(const float* query, const float* target, int b, int nq, int nt, float* dist, int32_t* idx,

@@ -205,8 +205,8 @@ def test_reference_smoke_script_semantics(cuda_lib, device):
     points1 = p1.clone().requires_grad_(True)  # leaf on the CPU, .cuda() makes a non-leaf (test.py:10-13)
     c1, c2 = points1.to(device), p2.to(device)
     dist1, dist2 = NND.nnd(c1, c2)
-    assert dist1.cpu().numpy().tobytes() == want_fwd[0].tobytes()
-    assert dist2.cpu().numpy().tobytes() == want_fwd[1].tobytes()
+    assert dist1.detach().cpu().numpy().tobytes() == want_fwd[0].tobytes()
+    assert dist2.detach().cpu().numpy().tobytes() == want_fwd[1].tobytes()
     torch.sum(dist1).backward()
     assert_grad_close((points1.grad.numpy(),), (want_g1,))
 
@@ -268,7 +268,8 @@ def test_non_contiguous_inputs_and_side_stream(cuda_lib, device):
     with torch.cuda.stream(s):
         d1, d2 = NND.nnd(a, b)
     s.synchronize()
-    assert d1.cpu().numpy().tobytes() == want[0].tobytes() and d2.cpu().numpy().tobytes() == want[1].tobytes()
+    assert d1.detach().cpu().numpy().tobytes() == want[0].tobytes()
+    assert d2.detach().cpu().numpy().tobytes() == want[1].tobytes()
 
 
 # ---------------------------------------------------------------- full-size configs: sampled-row exactness + properties
