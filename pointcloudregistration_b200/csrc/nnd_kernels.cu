@@ -37,6 +37,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "nnd_b200.h"
 
@@ -153,9 +154,10 @@ struct ScanParams {
 struct PrepCloud {
   const float* src;          // [b][n][3]
   float* soa;                // [b][tiles][3][TT]
-  unsigned long long* keys;  // [b][n] or nullptr
+  unsigned long long* keys;  // [b][n] (or [b][tiles*TT] when keys_padded) or nullptr
   int n, tiles;
   long long padded_total;  // b * tiles * TT
+  int keys_padded;
 };
 struct PrepParams {
   PrepCloud c[2];
@@ -196,7 +198,10 @@ __global__ void __launch_bounds__(256) nnd_prepare_kernel(PrepParams p) {
       d[0] = s[0];
       d[TT] = s[1];
       d[2 * TT] = s[2];
-      if (c.keys != nullptr && j < c.n) c.keys[batch * c.n + j] = ~0ull;
+      if (c.keys != nullptr) {
+        if (c.keys_padded) c.keys[g] = ~0ull;
+        else if (j < c.n) c.keys[batch * c.n + j] = ~0ull;
+      }
     }
   }
 }
@@ -393,6 +398,8 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
   }
 }
 
+#include "nnd_sym.cuh"
+
 // ----------------------------------------------------------------------------------
 // backward
 // ----------------------------------------------------------------------------------
@@ -512,6 +519,19 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 inline int tiles_of(int n) { return (n + kTT - 1) / kTT; }
 inline size_t soa_bytes(int b, int n) { return align_up((size_t)b * tiles_of(n) * 3 * kTT * sizeof(float), 256); }
 inline size_t key_bytes(int b, int n) { return align_up((size_t)b * n * sizeof(unsigned long long), 256); }
+inline size_t key_bytes_padded(int b, int n) {
+  return align_up((size_t)b * tiles_of(n) * kTT * sizeof(unsigned long long), 256);
+}
+
+// NND_B200_SYM=0 selects the two-pass forward (each direction scanned separately) for A/B measurements.
+bool use_symmetric() {
+  static int cached = -1;
+  if (cached < 0) {
+    const char* e = getenv("NND_B200_SYM");
+    cached = (e && e[0] == '0') ? 0 : 1;
+  }
+  return cached == 1;
+}
 
 void plan_dir(ScanDir& d, int b) {
   d.qtiles = tiles_of(d.nq);
@@ -532,7 +552,9 @@ int forward_impl(const float* c1, int n1, const float* c2, int n2, int b, int nd
   int rc = device_info(&di);
   if (rc) return rc;
   if (((uintptr_t)workspace & 255u) != 0) return NND_EWORKSPACE;
-  const size_t need = soa_bytes(b, n1) + soa_bytes(b, n2) + key_bytes(b, n1) + (ndir == 2 ? key_bytes(b, n2) : 0);
+  const bool sym = ndir == 2 && use_symmetric();
+  const size_t need =
+      soa_bytes(b, n1) + soa_bytes(b, n2) + key_bytes(b, n1) + (ndir == 2 ? key_bytes_padded(b, n2) : 0);
   if (workspace_bytes < need) return NND_EWORKSPACE;
   char* w = (char*)workspace;
   float* soa1 = (float*)w;
@@ -545,8 +567,8 @@ int forward_impl(const float* c1, int n1, const float* c2, int n2, int b, int nd
 
   PrepParams pp{};
   pp.nclouds = 2;
-  pp.c[0] = PrepCloud{c1, soa1, keys1, n1, tiles_of(n1), (long long)b * tiles_of(n1) * kTT};
-  pp.c[1] = PrepCloud{c2, soa2, keys2, n2, tiles_of(n2), (long long)b * tiles_of(n2) * kTT};
+  pp.c[0] = PrepCloud{c1, soa1, keys1, n1, tiles_of(n1), (long long)b * tiles_of(n1) * kTT, 0};
+  pp.c[1] = PrepCloud{c2, soa2, keys2, n2, tiles_of(n2), (long long)b * tiles_of(n2) * kTT, sym ? 1 : 0};
   {
     const long long total = pp.c[0].padded_total > pp.c[1].padded_total ? pp.c[0].padded_total : pp.c[1].padded_total;
     long long blocks = (total + 255) / 256;
@@ -558,6 +580,50 @@ int forward_impl(const float* c1, int n1, const float* c2, int n2, int b, int nd
   }
 
   const int grid_full = di.sms * kMinBlocks;
+  if (sym) {
+    // one evaluation of every distance serves both directions (nnd_sym.cuh)
+    SymParams yp{};
+    yp.qsoa = soa1;
+    yp.tsoa = soa2;
+    yp.rkeys = keys1;
+    yp.ckeys = keys2;
+    yp.n = n1;
+    yp.m = n2;
+    yp.qtiles = tiles_of(n1);
+    yp.ttiles = tiles_of(n2);
+    yp.qblocks = (n1 + kQB - 1) / kQB;
+    yp.total_units = (long long)b * yp.qblocks * yp.ttiles;
+    yp.one = 1.0f;
+    const int grid = yp.total_units < grid_full ? (int)yp.total_units : grid_full;
+    const size_t smem = sizeof(SymStage<kTT>) * kStages;
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_set[dev & 63]) {
+      cudaError_t e = cudaFuncSetAttribute(nnd_scan_sym_kernel<kThreads, kQPT, kTT, kChunk, kStages, kMinBlocks>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return (int)e;
+      attr_set[dev & 63] = true;
+    }
+    nnd_scan_sym_kernel<kThreads, kQPT, kTT, kChunk, kStages, kMinBlocks><<<grid, kThreads, smem, st>>>(yp);
+    ++g_launches;
+    if (ev) cudaEventRecord(ev[2], st);
+    FinParams fp{};
+    fp.ndir = 1;
+    fp.one = 1.0f;
+    fp.d[0] = FinDir{keys1, c1, soa2, dist1, idx1, n1, tiles_of(n2), (long long)b * n1};
+    long long blocks = (fp.d[0].count + 255) / 256;
+    if (blocks > (long long)di.sms * 16) blocks = (long long)di.sms * 16;
+    nnd_finalize_kernel<kTT, kChunk><<<(unsigned)blocks, 256, 0, st>>>(fp);
+    ++g_launches;
+    FinColParams cp{keys2, c1, c2, dist2, idx2, n1, n2, tiles_of(n2), (long long)b * n2, 1.0f};
+    blocks = (cp.count + 255) / 256;
+    if (blocks > (long long)di.sms * 16) blocks = (long long)di.sms * 16;
+    nnd_finalize_cols_kernel<kTT, kQPT><<<(unsigned)blocks, 256, 0, st>>>(cp);
+    ++g_launches;
+    if (ev) cudaEventRecord(ev[3], st);
+    return check_last(cudaGetLastError());
+  }
   ScanParams sp{};
   sp.ndir = ndir;
   sp.one = 1.0f;
@@ -639,7 +705,7 @@ const char* nnd_error_string(int code) {
 
 size_t nnd_workspace_bytes(int b, int n, int m) {
   if (b <= 0 || n <= 0 || m <= 0) return 256;
-  return soa_bytes(b, n) + soa_bytes(b, m) + key_bytes(b, n) + key_bytes(b, m);
+  return soa_bytes(b, n) + soa_bytes(b, m) + key_bytes(b, n) + key_bytes_padded(b, m);
 }
 
 size_t nnd_query_workspace_bytes(int b, int nq, int nt) {

@@ -1,0 +1,249 @@
+// nnd_sym.cuh -- included by nnd_kernels.cu inside its anonymous namespace.
+//
+// Symmetric forward: BOTH directions of nnd from ONE evaluation of every (xyz1[j], xyz2[k]) distance.
+//   dist1 direction computes fl(..(x2-x1)^2..) (my_lib.cpp:12-15 with query = xyz1), dist2 direction computes
+//   fl(..(x1-x2)^2..) (my_lib.cpp:57, roles swapped).  x1-x2 == -(x2-x1) exactly in IEEE arithmetic and the
+//   squares of a and -a are the same bits, so the two directions see bit-identical distance matrices: the
+//   row minima give dist1/idx1 and the column minima give dist2/idx2.
+//
+// Rows (xyz1 points, in registers) are handled exactly like nnd_scan_kernel: per-chunk minimum, first chunk wins,
+// key = (dist_bits << 32 | chunk_base), resolved by nnd_finalize_kernel.
+// Columns (xyz2 points, streamed through shared memory): every thread owns QPT CONSECUTIVE rows j = g*QPT .. g*QPT+QPT-1
+// ("group" g), so a smaller g means smaller row indices.  Per target the thread reduces its QPT distances to one
+// value c (3-input FMNMX tree).  The current global column key of every target travels with the tile (second TMA
+// copy) as a snapshot; only when some lane's c is <= the snapshot distance (rare once a target has seen a few
+// thousand rows) the warp takes the slow path: CREDUX.MIN over the lanes, lowest lane holding the minimum (=
+// lowest group) issues atomicMin(key = dist_bits << 32 | g) on the global key and on the shared-memory snapshot.
+// A stale snapshot is only ever too large, so no improvement or tie is missed.  nnd_finalize_cols_kernel resolves
+// the lowest row inside the winning group.
+
+struct SymParams {
+  const float* qsoa;          // xyz1 as SoA tiles [b][qtiles][3][TT]  (rows)
+  const float* tsoa;          // xyz2 as SoA tiles [b][ttiles][3][TT]  (columns)
+  unsigned long long* rkeys;  // [b][n]            (dist_bits << 32 | chunk_base)   pre-set to ~0
+  unsigned long long* ckeys;  // [b][ttiles * TT]  (dist_bits << 32 | row group)    pre-set to ~0
+  int n, m;
+  int qtiles, ttiles, qblocks;
+  long long total_units;  // b * qblocks * ttiles
+  float one;
+};
+
+struct FinColParams {
+  const unsigned long long* ckeys;  // [b][ttiles * TT]
+  const float* rows;                // xyz1 [b][n][3]
+  const float* cols;                // xyz2 [b][m][3]
+  float* dist;                      // dist2 [b][m]
+  int32_t* idx;                     // idx2  [b][m]
+  int n, m, ttiles;
+  long long count;  // b * m
+  float one;
+};
+
+template <int TT>
+struct __align__(128) SymStage {
+  float xyz[3 * TT];
+  unsigned long long snap[TT];
+};
+
+template <int THREADS, int QPT, int TT, int C, int STAGES, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __grid_constant__ SymParams p) {
+  static_assert(TT % C == 0 && C % 4 == 0 && QPT % 2 == 0 && TT % QPT == 0, "tile/chunk shape");
+  constexpr int QB = THREADS * QPT;
+  constexpr uint32_t XYZ_BYTES = 3 * TT * sizeof(float);
+  constexpr uint32_t SNAP_BYTES = TT * sizeof(unsigned long long);
+  constexpr unsigned FULL = 0xffffffffu;
+  extern __shared__ __align__(128) unsigned char sym_smem[];
+  SymStage<TT>* stages = reinterpret_cast<SymStage<TT>*>(sym_smem);
+  __shared__ __align__(8) uint64_t full[STAGES];
+
+  const int tid = threadIdx.x;
+  const unsigned lane = tid & 31u;
+  const long long u_begin = p.total_units * blockIdx.x / gridDim.x;
+  const long long u_end = p.total_units * (blockIdx.x + 1) / gridDim.x;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  long long pu = u_begin;  // producer cursor (thread 0)
+  auto produce = [&](int stage) {
+    const long long qb = pu / p.ttiles;
+    const int tile = (int)(pu - qb * p.ttiles);
+    const long long batch = qb / p.qblocks;
+    const long long t = batch * p.ttiles + tile;
+    mbar_expect_tx(&full[stage], XYZ_BYTES + SNAP_BYTES);
+    tma_load_1d(stages[stage].xyz, p.tsoa + t * (3 * TT), XYZ_BYTES, &full[stage]);
+    tma_load_1d(stages[stage].snap, p.ckeys + t * TT, SNAP_BYTES, &full[stage]);
+    ++pu;
+  };
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s)
+      if (pu < u_end) produce(s);
+  }
+
+  const uint64_t one = pk2(p.one, p.one);
+  const float INF = __int_as_float(0x7f800000);
+  uint32_t cnt = 0;
+
+  long long u = u_begin;
+  while (u < u_end) {
+    const long long qbg = u / p.ttiles;
+    const int tile0 = (int)(u - qbg * p.ttiles);
+    const int batch = (int)(qbg / p.qblocks);
+    const int qblock = (int)(qbg - (long long)batch * p.qblocks);
+    const long long rest = (long long)p.ttiles - tile0;
+    const int seg_tiles = (int)(u_end - u < rest ? u_end - u : rest);
+
+    // ---- rows -> registers: QPT consecutive rows per thread
+    uint64_t nqx[QPT], nqy[QPT], nqz[QPT];
+    float best[QPT];
+    int bchunk[QPT];
+    const unsigned group = (unsigned)(qblock * THREADS + tid);  // row group id inside this batch element
+    const float* qbase = p.qsoa + (long long)batch * p.qtiles * (3 * TT);
+#pragma unroll
+    for (int q = 0; q < QPT; ++q) {
+      int j = qblock * QB + tid * QPT + q;
+      j = j < p.n ? j : p.n - 1;
+      const int qt = j / TT, qo = j - qt * TT;
+      const float* s = qbase + (long long)qt * (3 * TT) + qo;
+      const float x = -s[0], y = -s[TT], z = -s[2 * TT];
+      nqx[q] = pk2(x, x);
+      nqy[q] = pk2(y, y);
+      nqz[q] = pk2(z, z);
+      best[q] = INF;
+      bchunk[q] = 0;
+    }
+    unsigned long long* ckeys = p.ckeys + (long long)batch * p.ttiles * TT;
+
+    for (int tile = tile0; tile < tile0 + seg_tiles; ++tile) {
+      const int stage = cnt % STAGES;
+      mbar_wait(&full[stage], (cnt / STAGES) & 1);
+      const float* sx = stages[stage].xyz;
+      const float* sy = sx + TT;
+      const float* sz = sx + 2 * TT;
+      unsigned long long* snap = stages[stage].snap;
+      const int valid = min(TT, p.m - tile * TT);
+      const int nchunks = (valid + C - 1) / C;
+
+      for (int ch = 0; ch < nchunks; ++ch) {
+        const ulonglong2* cx = reinterpret_cast<const ulonglong2*>(sx + ch * C);
+        const ulonglong2* cy = reinterpret_cast<const ulonglong2*>(sy + ch * C);
+        const ulonglong2* cz = reinterpret_cast<const ulonglong2*>(sz + ch * C);
+        float cm[QPT];
+#pragma unroll
+        for (int q = 0; q < QPT; ++q) cm[q] = INF;
+#pragma unroll
+        for (int s4 = 0; s4 < C / 4; ++s4) {
+          const ulonglong2 X = cx[s4], Y = cy[s4], Z = cz[s4];
+          float c0 = INF, c1 = INF, c2 = INF, c3 = INF;  // column minima over this thread's rows
+#pragma unroll
+          for (int q = 0; q < QPT; q += 2) {
+            float a0, a1, b0, b1, e0, e1, f0, f1;
+            upk2(sqdist2(X.x, Y.x, Z.x, nqx[q], nqy[q], nqz[q], one), a0, a1);
+            upk2(sqdist2(X.y, Y.y, Z.y, nqx[q], nqy[q], nqz[q], one), b0, b1);
+            upk2(sqdist2(X.x, Y.x, Z.x, nqx[q + 1], nqy[q + 1], nqz[q + 1], one), e0, e1);
+            upk2(sqdist2(X.y, Y.y, Z.y, nqx[q + 1], nqy[q + 1], nqz[q + 1], one), f0, f1);
+            cm[q] = fmin3(cm[q], a0, a1);
+            cm[q] = fmin3(cm[q], b0, b1);
+            cm[q + 1] = fmin3(cm[q + 1], e0, e1);
+            cm[q + 1] = fmin3(cm[q + 1], f0, f1);
+            c0 = fmin3(c0, a0, e0);
+            c1 = fmin3(c1, a1, e1);
+            c2 = fmin3(c2, b0, f0);
+            c3 = fmin3(c3, b1, f1);
+          }
+          // ---- columns: compare with the snapshot of the global keys (high word = distance bits)
+          const int koff = ch * C + 4 * s4;
+          const ulonglong2 K01 = *reinterpret_cast<const ulonglong2*>(snap + koff);
+          const ulonglong2 K23 = *reinterpret_cast<const ulonglong2*>(snap + koff + 2);
+          const unsigned h0 = (unsigned)(K01.x >> 32), h1 = (unsigned)(K01.y >> 32);
+          const unsigned h2 = (unsigned)(K23.x >> 32), h3 = (unsigned)(K23.y >> 32);
+          const unsigned u0 = __float_as_uint(c0), u1 = __float_as_uint(c1);
+          const unsigned u2 = __float_as_uint(c2), u3 = __float_as_uint(c3);
+          const bool ev = (u0 <= h0) | (u1 <= h1) | (u2 <= h2) | (u3 <= h3);
+          if (__any_sync(FULL, ev)) {
+            const unsigned uu[4] = {u0, u1, u2, u3};
+            const unsigned hh[4] = {h0, h1, h2, h3};
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const unsigned mn = __reduce_min_sync(FULL, uu[t]);
+              if (mn <= hh[t]) {  // warp-uniform
+                const unsigned holders = __ballot_sync(FULL, uu[t] == mn);
+                if (lane == (unsigned)(__ffs(holders) - 1)) {  // lowest lane = lowest row group
+                  const unsigned long long key = ((unsigned long long)mn << 32) | group;
+                  atomicMin(ckeys + (long long)tile * TT + koff + t, key);
+                  atomicMin(snap + koff + t, key);
+                }
+              }
+            }
+          }
+        }
+        const int cbase = tile * TT + ch * C;
+#pragma unroll
+        for (int q = 0; q < QPT; ++q) {
+          if (cm[q] < best[q]) bchunk[q] = cbase;
+          best[q] = fminf(best[q], cm[q]);
+        }
+      }
+
+      __syncthreads();
+      if (tid == 0 && pu < u_end) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        produce(stage);
+      }
+      ++cnt;
+    }
+
+    unsigned long long* rkeys = p.rkeys + (long long)batch * p.n;
+#pragma unroll
+    for (int q = 0; q < QPT; ++q) {
+      const int j = qblock * QB + tid * QPT + q;
+      if (j < p.n) {
+        const unsigned long long key =
+            ((unsigned long long)__float_as_uint(best[q]) << 32) | (unsigned long long)(unsigned)bchunk[q];
+        atomicMin(rkeys + j, key);
+      }
+    }
+    u += seg_tiles;
+  }
+}
+
+// Column finalize: key = (dist_bits << 32 | row group).  Re-evaluate the QPT rows of the group against this
+// column point with the same packed sequence and take the lowest row with d == dist.
+template <int TT, int QPT>
+__global__ void __launch_bounds__(256) nnd_finalize_cols_kernel(FinColParams p) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const uint64_t one = pk2(p.one, p.one);
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < p.count; g += stride) {
+    const long long batch = g / p.m;
+    const int k = (int)(g - batch * p.m);
+    const unsigned long long key = p.ckeys[batch * p.ttiles * TT + k];
+    const float bq = __uint_as_float((unsigned)(key >> 32));
+    const long long j0 = (long long)(unsigned)(key & 0xffffffffull) * QPT;
+    const float* t = p.cols + g * 3;
+    const uint64_t TX = pk2(t[0], t[0]), TY = pk2(t[1], t[1]), TZ = pk2(t[2], t[2]);
+    const float* rows = p.rows + batch * p.n * 3;
+    int found = 0;
+#pragma unroll
+    for (int q = QPT - 2; q >= 0; q -= 2) {  // descending: the last hit is the lowest row
+      long long ja = j0 + q, jb = j0 + q + 1;
+      ja = ja < p.n ? ja : p.n - 1;
+      jb = jb < p.n ? jb : p.n - 1;
+      const float* ra = rows + ja * 3;
+      const float* rb = rows + jb * 3;
+      const uint64_t dd = sqdist2(TX, TY, TZ, pk2(-ra[0], -rb[0]), pk2(-ra[1], -rb[1]), pk2(-ra[2], -rb[2]), one);
+      float lo, hi;
+      upk2(dd, lo, hi);
+      if (hi == bq) found = q + 1;
+      if (lo == bq) found = q;
+    }
+    long long j = j0 + found;
+    j = j < p.n ? j : p.n - 1;
+    p.dist[g] = bq;
+    p.idx[g] = (int32_t)j;
+  }
+}
