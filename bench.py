@@ -321,10 +321,16 @@ def run_b200_arm(args, w):
         cpu_base, _ = cpu_arm(w, 1, 0, args.cpu_seconds, kind)
 
     if rank == 0:
-        scan_calls_per_step = 1 if world == 1 else 2
+        # One launch of the symmetric scan kernel evaluates every (xyz1[j], xyz2[k]) distance of its row range
+        # ONCE and serves both directions from it (row minima -> dist1/idx1, column minima -> dist2/idx2), so a
+        # launch EXECUTES b*n*m/world distance evaluations = half of the metric's `pairs` (2*b*n*m counts each
+        # distance once per direction).  roofline.achieved/frac count the evaluations actually executed
+        # (8 FP32 ops each) -- the honest pipe utilisation; `metric_equivalent_*` credits the launch with the
+        # 2 pairs per evaluation it delivers (what the two-pass reference formulation would have had to execute).
+        scan_calls_per_step = 1
         scan_ms_avg = scan_ms_total / (steps * scan_calls_per_step)  # average launch duration
-        scan_pairs = pairs / world / scan_calls_per_step  # pairs one launch on one GPU evaluates
-        achieved = scan_pairs * FP32_OPS_PER_PAIR / (scan_ms_avg * 1e-3) / 1e12
+        scan_evals = pairs / 2 / world  # distance evaluations one launch on one GPU executes
+        achieved = scan_evals * FP32_OPS_PER_PAIR / (scan_ms_avg * 1e-3) / 1e12
         peak = fp32_peak / 1e12
         traffic = None
         tfile = ROOT / "profiles" / "scan_traffic.json"
@@ -339,12 +345,15 @@ def run_b200_arm(args, w):
                        "pairs_per_step": pairs, "l2": "256 MB buffer rewritten between timed steps (L2 flush)",
                        "parallelism": "query rows sharded over ranks; NCCL broadcast of both clouds, all_gather of "
                                       "dist/idx, all_reduce of gradients" if world > 1 else "single GPU"},
-            "roofline": {"bound": "fp32", "kernel": "nnd_scan_kernel", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "fp32", "kernel": "nnd_scan_sym_kernel", "achieved": achieved, "peak": peak,
                          "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                          "peak_source": f"148 SM x 128 FP32 lanes x sm_max_mhz {sm_max_mhz:.0f} MHz, {peak_src}; FMA is "
                                         "forbidden by bit-exactness so 1 op = 1 lane-slot (the FMA-flop peak is 2x)",
                          "frac_of_fma_flop_peak": achieved / (2 * peak),
-                         "flop_per_launch": scan_pairs * FP32_OPS_PER_PAIR, "kernel_ms": scan_ms_avg,
+                         "flop_per_launch": scan_evals * FP32_OPS_PER_PAIR, "kernel_ms": scan_ms_avg,
+                         "evaluations_per_launch": scan_evals, "metric_pairs_per_launch": 2 * scan_evals,
+                         "metric_equivalent_achieved": 2 * achieved, "metric_equivalent_frac": 2 * achieved / peak,
+                         "metric_equivalent_frac_of_fma_flop_peak": achieved / peak,
                          "kernel_share_of_step": scan_ms_total / world / total_ms if world == 1 else None},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": float(e2e_ms.item()) / steps, "loss": last_loss},

@@ -49,6 +49,27 @@ const char *nnd_error_string(int code);
  * The workspace must be 256-byte aligned device memory. */
 size_t nnd_workspace_bytes(int b, int n, int m);
 
+/* ---- row-range forward: the unit the multi-GPU path calls (new design; the
+ * reference has no multi-device path).  One evaluation of every (xyz1[j], xyz2[k]) distance serves both
+ * directions, so a rank that owns rows [row_lo, row_hi) of xyz1 produces
+ *   - dist1/idx1 for its rows (final), written into the FULL-SIZE [b,n] buffers at those rows only, and
+ *   - colkeys[b * nnd_colkeys_count(1, m)]: for every point of xyz2 the packed partial result
+ *     (float_bits(dist) << 32 | row_group) over this rank's rows.  Keys of different ranks merge with an
+ *     element-wise integer MIN (every key is < 2^63: signed and unsigned order agree), e.g. an NCCL
+ *     all-reduce(MIN) on int64; nnd_finalize_cols_cuda_f32 then turns merged keys into dist2/idx2.
+ * row_lo must be a multiple of nnd_row_group(); row_hi must be one too unless row_hi == n.
+ * nnd_forward_cuda_f32 is exactly rows [0, n) followed by the column finalize. */
+size_t nnd_rows_workspace_bytes(int b, int n, int m);
+size_t nnd_colkeys_count(int b, int m);
+int nnd_row_group(void);
+int nnd_forward_rows_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int m,
+                              int row_lo, int row_hi, float *dist1, int32_t *idx1,
+                              unsigned long long *colkeys,
+                              void *workspace, size_t workspace_bytes, void *stream);
+int nnd_finalize_cols_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int m,
+                               const unsigned long long *colkeys,
+                               float *dist2, int32_t *idx2, void *stream);
+
 /* Scratch bytes needed by nnd_query_cuda_f32 (one direction). */
 size_t nnd_query_workspace_bytes(int b, int nq, int nt);
 

@@ -89,6 +89,11 @@ __device__ __forceinline__ float fmin_xs(float a, float b) {
   return r;
 }
 
+// 3-input minimum on the bit patterns as signed integers (for operands >= +0 this is the float minimum)
+__device__ __forceinline__ float imin3f(float a, float b, float c) {
+  return __int_as_float(min(min(__float_as_int(a), __float_as_int(b)), __float_as_int(c)));
+}
+
 // Two squared distances at once.  T* = {t[k], t[k+1]}, nq* = {-q, -q}, one = {1.0f, 1.0f}
 // passed at run time.  Every operation rounds separately (my_lib.cpp:12-15).
 __device__ __forceinline__ uint64_t sqdist2(uint64_t TX, uint64_t TY, uint64_t TZ, uint64_t nqx,
@@ -152,26 +157,33 @@ struct ScanParams {
 };
 
 struct PrepCloud {
-  const float* src;          // [b][n][3]
-  float* soa;                // [b][tiles][3][TT]
-  unsigned long long* keys;  // [b][n] (or [b][tiles*TT] when keys_padded) or nullptr
+  const float* src;  // [b][n][3]
+  float* soa;        // [b][tiles][3][TT]
   int n, tiles;
   long long padded_total;  // b * tiles * TT
-  int keys_padded;
 };
 struct PrepParams {
   PrepCloud c[2];
   int nclouds;
+  unsigned long long* fill64[2];  // key arrays set to kKeyInit
+  long long count64[2];
+  unsigned* fill32;  // column filter set to 0xffffffff
+  long long count32;
 };
+
+// Initial value of every packed key.  Larger than any (dist_bits << 32 | x) with dist_bits <= 0x7fffffff, and
+// positive as a SIGNED 64-bit integer, so per-rank column keys can be merged with an int64 MIN all-reduce.
+constexpr unsigned long long kKeyInit = 0x7fffffffffffffffull;
 
 struct FinDir {
   const unsigned long long* keys;  // [b][nq]
   const float* q;                  // [b][nq][3] original query cloud (AoS)
   const float* tsoa;               // [b][ttiles][3][TT]
-  float* dist;
-  int32_t* idx;
+  float* dist;                     // [b][nq]
+  int32_t* idx;                    // [b][nq]
   int nq, ttiles;
-  long long count;  // b * nq
+  int row_lo, nrows;  // rows [row_lo, row_lo + nrows) of every batch element are finalized
+  long long count;    // b * nrows
 };
 struct FinParams {
   FinDir d[2];
@@ -185,10 +197,11 @@ struct FinParams {
 template <int TT>
 __global__ void __launch_bounds__(256) nnd_prepare_kernel(PrepParams p) {
   const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   for (int ci = 0; ci < p.nclouds; ++ci) {
     const PrepCloud c = p.c[ci];
     const long long per_batch = (long long)c.tiles * TT;
-    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < c.padded_total; g += stride) {
+    for (long long g = first; g < c.padded_total; g += stride) {
       const long long batch = g / per_batch;
       const int j = (int)(g - batch * per_batch);
       const int tile = j / TT, off = j - tile * TT;
@@ -198,12 +211,12 @@ __global__ void __launch_bounds__(256) nnd_prepare_kernel(PrepParams p) {
       d[0] = s[0];
       d[TT] = s[1];
       d[2 * TT] = s[2];
-      if (c.keys != nullptr) {
-        if (c.keys_padded) c.keys[g] = ~0ull;
-        else if (j < c.n) c.keys[batch * c.n + j] = ~0ull;
-      }
     }
   }
+#pragma unroll
+  for (int k = 0; k < 2; ++k)
+    for (long long g = first; g < p.count64[k]; g += stride) p.fill64[k][g] = kKeyInit;
+  for (long long g = first; g < p.count32; g += stride) p.fill32[g] = 0xffffffffu;
 }
 
 // ----------------------------------------------------------------------------------
@@ -217,11 +230,12 @@ __global__ void __launch_bounds__(256) nnd_finalize_kernel(FinParams p) {
   const uint64_t one = pk2(p.one, p.one);
   for (int di = 0; di < p.ndir; ++di) {
     const FinDir d = p.d[di];
-    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < d.count; g += stride) {
+    for (long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x; w < d.count; w += stride) {
+      const long long batch = w / d.nrows;
+      const long long g = batch * d.nq + d.row_lo + (w - batch * d.nrows);  // flat [b][nq] index of this row
       const unsigned long long key = d.keys[g];
       const float bq = __uint_as_float((unsigned)(key >> 32));
       const int base = (int)(unsigned)(key & 0xffffffffull);
-      const long long batch = g / d.nq;
       const float* qp = d.q + g * 3;
       const float x = -qp[0], y = -qp[1], z = -qp[2];
       const uint64_t nqx = pk2(x, x), nqy = pk2(y, y), nqz = pk2(z, z);
@@ -473,12 +487,27 @@ __global__ void __launch_bounds__(256) nnd_grad_kernel(GradParams p) {
 // ----------------------------------------------------------------------------------
 // host side
 // ----------------------------------------------------------------------------------
-constexpr int kThreads = 256;
-constexpr int kQPT = 8;
+#ifndef NND_THREADS
+#define NND_THREADS 256
+#endif
+#ifndef NND_QPT
+#define NND_QPT 8
+#endif
+#ifndef NND_MINB
+#define NND_MINB 2
+#endif
+#ifndef NND_STAGES
+#define NND_STAGES 4
+#endif
+constexpr int kThreads = NND_THREADS;
+constexpr int kQPT = NND_QPT;
 constexpr int kTT = 512;
-constexpr int kChunk = 32;
-constexpr int kStages = 4;
-constexpr int kMinBlocks = 2;
+#ifndef NND_CHUNK
+#define NND_CHUNK 32
+#endif
+constexpr int kChunk = NND_CHUNK;
+constexpr int kStages = NND_STAGES;
+constexpr int kMinBlocks = NND_MINB;
 constexpr int kQB = kThreads * kQPT;
 
 thread_local int g_launches = 0;
@@ -519,146 +548,194 @@ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 inline int tiles_of(int n) { return (n + kTT - 1) / kTT; }
 inline size_t soa_bytes(int b, int n) { return align_up((size_t)b * tiles_of(n) * 3 * kTT * sizeof(float), 256); }
 inline size_t key_bytes(int b, int n) { return align_up((size_t)b * n * sizeof(unsigned long long), 256); }
-inline size_t key_bytes_padded(int b, int n) {
-  return align_up((size_t)b * tiles_of(n) * kTT * sizeof(unsigned long long), 256);
-}
-
-// NND_B200_SYM=0 selects the two-pass forward (each direction scanned separately) for A/B measurements.
-bool use_symmetric() {
-  static int cached = -1;
-  if (cached < 0) {
-    const char* e = getenv("NND_B200_SYM");
-    cached = (e && e[0] == '0') ? 0 : 1;
-  }
-  return cached == 1;
-}
-
-void plan_dir(ScanDir& d, int b) {
-  d.qtiles = tiles_of(d.nq);
-  d.ttiles = tiles_of(d.nt);
-  d.qblocks = (d.nq + kQB - 1) / kQB;
-  d.units = (long long)b * d.qblocks * d.ttiles;
-}
+inline size_t colkey_count(int b, int m) { return (size_t)b * tiles_of(m) * kTT; }
+inline size_t colkey_bytes(int b, int m) { return align_up(colkey_count(b, m) * sizeof(unsigned long long), 256); }
+inline size_t filter_bytes(int b, int m) { return align_up(colkey_count(b, m) * sizeof(unsigned), 256); }
 
 int check_last(cudaError_t e) { return e == cudaSuccess ? 0 : (int)e; }
 
-// Runs prepare + scan + finalize for one or two directions.
-// dirs: (query cloud, nq, target cloud, nt, dist, idx); ndir == 2 means the two clouds swap roles.
-int forward_impl(const float* c1, int n1, const float* c2, int n2, int b, int ndir, float* dist1, int32_t* idx1,
-                 float* dist2, int32_t* idx2, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+// NND_B200_DEBUG_SYNC=1: synchronise after every kernel of the forward and report it on stderr (triage aid).
+void debug_sync(const char* what, cudaStream_t st) {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("NND_B200_DEBUG_SYNC");
+    on = (e && e[0] == '1') ? 1 : 0;
+  }
+  if (!on) return;
+  fprintf(stderr, "[nnd] %s launched...\n", what);
+  fflush(stderr);
+  cudaError_t e = cudaStreamSynchronize(st);
+  fprintf(stderr, "[nnd] %s done: %s\n", what, cudaGetErrorString(e));
+  fflush(stderr);
+}
+
+inline unsigned grid_for(long long items, int sms) {
+  long long blocks = (items + 255) / 256;
+  if (blocks > (long long)sms * 16) blocks = (long long)sms * 16;
+  return (unsigned)(blocks < 1 ? 1 : blocks);
+}
+
+// Symmetric forward over the row range [row_lo, row_hi) of xyz1 (every batch element):
+//   prepare (SoA copies, key/filter init) -> nnd_scan_sym_kernel -> nnd_finalize_kernel for those rows.
+// colkeys receives this launch's column keys; finalize_cols_impl turns (merged) column keys into dist2/idx2.
+int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, int row_lo, int row_hi, float* dist1,
+                      int32_t* idx1, unsigned long long* colkeys, void* workspace, size_t workspace_bytes,
+                      cudaStream_t st) {
   cudaEvent_t* ev = nullptr;
   if (g_prof.enabled && g_prof.used < kProfSlots) ev = &g_prof.ev[4 * g_prof.used++];
   DeviceInfo di;
   int rc = device_info(&di);
   if (rc) return rc;
   if (((uintptr_t)workspace & 255u) != 0) return NND_EWORKSPACE;
-  const bool sym = ndir == 2 && use_symmetric();
-  const size_t need =
-      soa_bytes(b, n1) + soa_bytes(b, n2) + key_bytes(b, n1) + (ndir == 2 ? key_bytes_padded(b, n2) : 0);
+  const size_t need = soa_bytes(b, n1) + soa_bytes(b, n2) + key_bytes(b, n1) + filter_bytes(b, n2);
   if (workspace_bytes < need) return NND_EWORKSPACE;
   char* w = (char*)workspace;
   float* soa1 = (float*)w;
   w += soa_bytes(b, n1);
   float* soa2 = (float*)w;
   w += soa_bytes(b, n2);
-  unsigned long long* keys1 = (unsigned long long*)w;
+  unsigned long long* rkeys = (unsigned long long*)w;
   w += key_bytes(b, n1);
-  unsigned long long* keys2 = ndir == 2 ? (unsigned long long*)w : nullptr;
+  unsigned* cdist = (unsigned*)w;
+  const int nrows = row_hi - row_lo;
+
+  PrepParams pp{};
+  pp.nclouds = nrows > 0 ? 2 : 0;
+  pp.c[0] = PrepCloud{c1, soa1, n1, tiles_of(n1), (long long)b * tiles_of(n1) * kTT};
+  pp.c[1] = PrepCloud{c2, soa2, n2, tiles_of(n2), (long long)b * tiles_of(n2) * kTT};
+  pp.fill64[0] = rkeys;
+  pp.count64[0] = nrows > 0 ? (long long)b * n1 : 0;
+  pp.fill64[1] = colkeys;
+  pp.count64[1] = (long long)colkey_count(b, n2);
+  pp.fill32 = cdist;
+  pp.count32 = nrows > 0 ? (long long)colkey_count(b, n2) : 0;
+  {
+    long long total = pp.c[0].padded_total > pp.c[1].padded_total ? pp.c[0].padded_total : pp.c[1].padded_total;
+    if (ev) cudaEventRecord(ev[0], st);
+    nnd_prepare_kernel<kTT><<<grid_for(total, di.sms), 256, 0, st>>>(pp);
+    ++g_launches;
+    if (ev) cudaEventRecord(ev[1], st);
+    debug_sync("prepare", st);
+  }
+  if (nrows <= 0) {  // nothing to scan: the column keys stay at their initial value
+    if (ev) {
+      cudaEventRecord(ev[2], st);
+      cudaEventRecord(ev[3], st);
+    }
+    return check_last(cudaGetLastError());
+  }
+
+  SymParams yp{};
+  yp.qsoa = soa1;
+  yp.tsoa = soa2;
+  yp.rkeys = rkeys;
+  yp.ckeys = colkeys;
+  yp.cdist = cdist;
+  yp.n = n1;
+  yp.m = n2;
+  yp.row_lo = row_lo;
+  yp.row_hi = row_hi;
+  yp.qtiles = tiles_of(n1);
+  yp.ttiles = tiles_of(n2);
+  yp.qblocks = (nrows + kQB - 1) / kQB;
+  yp.total_units = (long long)b * yp.qblocks * yp.ttiles;
+  yp.one = 1.0f;
+  const int grid_full = di.sms * kMinBlocks;
+  const int grid = yp.total_units < grid_full ? (int)yp.total_units : grid_full;
+  const size_t smem = sizeof(SymStage<kTT>) * kStages;
+  static bool attr_set[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(nnd_scan_sym_kernel<kThreads, kQPT, kTT, kChunk, kStages, kMinBlocks>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    attr_set[dev & 63] = true;
+  }
+  nnd_scan_sym_kernel<kThreads, kQPT, kTT, kChunk, kStages, kMinBlocks><<<grid, kThreads, smem, st>>>(yp);
+  ++g_launches;
+  if (ev) cudaEventRecord(ev[2], st);
+  debug_sync("scan_sym", st);
+
+  FinParams fp{};
+  fp.ndir = 1;
+  fp.one = 1.0f;
+  fp.d[0] = FinDir{rkeys, c1, soa2, dist1, idx1, n1, tiles_of(n2), row_lo, nrows, (long long)b * nrows};
+  nnd_finalize_kernel<kTT, kChunk><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
+  ++g_launches;
+  if (ev) cudaEventRecord(ev[3], st);
+  debug_sync("finalize_rows", st);
+  return check_last(cudaGetLastError());
+}
+
+int finalize_cols_impl(const float* c1, int n1, const float* c2, int n2, int b, const unsigned long long* colkeys,
+                       float* dist2, int32_t* idx2, cudaStream_t st) {
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  FinColParams cp{colkeys, c1, c2, dist2, idx2, n1, n2, tiles_of(n2), (long long)b * n2, 1.0f};
+  nnd_finalize_cols_kernel<kTT, kQPT><<<grid_for(cp.count, di.sms), 256, 0, st>>>(cp);
+  ++g_launches;
+  debug_sync("finalize_cols", st);
+  return check_last(cudaGetLastError());
+}
+
+// One direction (nnd_query_cuda_f32): prepare + nnd_scan_kernel + finalize.
+int query_impl(const float* q, int nq, const float* t, int nt, int b, float* dist, int32_t* idx, void* workspace,
+               size_t workspace_bytes, cudaStream_t st) {
+  cudaEvent_t* ev = nullptr;
+  if (g_prof.enabled && g_prof.used < kProfSlots) ev = &g_prof.ev[4 * g_prof.used++];
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  if (((uintptr_t)workspace & 255u) != 0) return NND_EWORKSPACE;
+  const size_t need = soa_bytes(b, nq) + soa_bytes(b, nt) + key_bytes(b, nq);
+  if (workspace_bytes < need) return NND_EWORKSPACE;
+  char* w = (char*)workspace;
+  float* soaq = (float*)w;
+  w += soa_bytes(b, nq);
+  float* soat = (float*)w;
+  w += soa_bytes(b, nt);
+  unsigned long long* keys = (unsigned long long*)w;
 
   PrepParams pp{};
   pp.nclouds = 2;
-  pp.c[0] = PrepCloud{c1, soa1, keys1, n1, tiles_of(n1), (long long)b * tiles_of(n1) * kTT, 0};
-  pp.c[1] = PrepCloud{c2, soa2, keys2, n2, tiles_of(n2), (long long)b * tiles_of(n2) * kTT, sym ? 1 : 0};
+  pp.c[0] = PrepCloud{q, soaq, nq, tiles_of(nq), (long long)b * tiles_of(nq) * kTT};
+  pp.c[1] = PrepCloud{t, soat, nt, tiles_of(nt), (long long)b * tiles_of(nt) * kTT};
+  pp.fill64[0] = keys;
+  pp.count64[0] = (long long)b * nq;
   {
-    const long long total = pp.c[0].padded_total > pp.c[1].padded_total ? pp.c[0].padded_total : pp.c[1].padded_total;
-    long long blocks = (total + 255) / 256;
-    if (blocks > (long long)di.sms * 16) blocks = (long long)di.sms * 16;
+    long long total = pp.c[0].padded_total > pp.c[1].padded_total ? pp.c[0].padded_total : pp.c[1].padded_total;
     if (ev) cudaEventRecord(ev[0], st);
-    nnd_prepare_kernel<kTT><<<(unsigned)blocks, 256, 0, st>>>(pp);
+    nnd_prepare_kernel<kTT><<<grid_for(total, di.sms), 256, 0, st>>>(pp);
     ++g_launches;
     if (ev) cudaEventRecord(ev[1], st);
   }
-
-  const int grid_full = di.sms * kMinBlocks;
-  if (sym) {
-    // one evaluation of every distance serves both directions (nnd_sym.cuh)
-    SymParams yp{};
-    yp.qsoa = soa1;
-    yp.tsoa = soa2;
-    yp.rkeys = keys1;
-    yp.ckeys = keys2;
-    yp.n = n1;
-    yp.m = n2;
-    yp.qtiles = tiles_of(n1);
-    yp.ttiles = tiles_of(n2);
-    yp.qblocks = (n1 + kQB - 1) / kQB;
-    yp.total_units = (long long)b * yp.qblocks * yp.ttiles;
-    yp.one = 1.0f;
-    const int grid = yp.total_units < grid_full ? (int)yp.total_units : grid_full;
-    const size_t smem = sizeof(SymStage<kTT>) * kStages;
-    static bool attr_set[64] = {};
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (!attr_set[dev & 63]) {
-      cudaError_t e = cudaFuncSetAttribute(nnd_scan_sym_kernel<kThreads, kQPT, kTT, kChunk, kStages, kMinBlocks>,
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e != cudaSuccess) return (int)e;
-      attr_set[dev & 63] = true;
-    }
-    nnd_scan_sym_kernel<kThreads, kQPT, kTT, kChunk, kStages, kMinBlocks><<<grid, kThreads, smem, st>>>(yp);
-    ++g_launches;
-    if (ev) cudaEventRecord(ev[2], st);
-    FinParams fp{};
-    fp.ndir = 1;
-    fp.one = 1.0f;
-    fp.d[0] = FinDir{keys1, c1, soa2, dist1, idx1, n1, tiles_of(n2), (long long)b * n1};
-    long long blocks = (fp.d[0].count + 255) / 256;
-    if (blocks > (long long)di.sms * 16) blocks = (long long)di.sms * 16;
-    nnd_finalize_kernel<kTT, kChunk><<<(unsigned)blocks, 256, 0, st>>>(fp);
-    ++g_launches;
-    FinColParams cp{keys2, c1, c2, dist2, idx2, n1, n2, tiles_of(n2), (long long)b * n2, 1.0f};
-    blocks = (cp.count + 255) / 256;
-    if (blocks > (long long)di.sms * 16) blocks = (long long)di.sms * 16;
-    nnd_finalize_cols_kernel<kTT, kQPT><<<(unsigned)blocks, 256, 0, st>>>(cp);
-    ++g_launches;
-    if (ev) cudaEventRecord(ev[3], st);
-    return check_last(cudaGetLastError());
-  }
   ScanParams sp{};
-  sp.ndir = ndir;
+  sp.ndir = 1;
   sp.one = 1.0f;
-  sp.d[0].qsoa = soa1;
-  sp.d[0].tsoa = soa2;
-  sp.d[0].keys = keys1;
-  sp.d[0].nq = n1;
-  sp.d[0].nt = n2;
-  if (ndir == 2) {
-    sp.d[1].qsoa = soa2;
-    sp.d[1].tsoa = soa1;
-    sp.d[1].keys = keys2;
-    sp.d[1].nq = n2;
-    sp.d[1].nt = n1;
-  }
-  for (int i = 0; i < ndir; ++i) plan_dir(sp.d[i], b);
-  sp.total_units = sp.d[0].units + (ndir == 2 ? sp.d[1].units : 0);
+  sp.d[0].qsoa = soaq;
+  sp.d[0].tsoa = soat;
+  sp.d[0].keys = keys;
+  sp.d[0].nq = nq;
+  sp.d[0].nt = nt;
+  sp.d[0].qtiles = tiles_of(nq);
+  sp.d[0].ttiles = tiles_of(nt);
+  sp.d[0].qblocks = (nq + kQB - 1) / kQB;
+  sp.d[0].units = (long long)b * sp.d[0].qblocks * sp.d[0].ttiles;
+  sp.total_units = sp.d[0].units;
+  const int grid_full = di.sms * kMinBlocks;
   const int grid = sp.total_units < grid_full ? (int)sp.total_units : grid_full;
   nnd_scan_kernel<kThreads, kQPT, kTT, kChunk, kStages, kMinBlocks><<<grid, kThreads, 0, st>>>(sp);
   ++g_launches;
   if (ev) cudaEventRecord(ev[2], st);
-
   FinParams fp{};
-  fp.ndir = ndir;
+  fp.ndir = 1;
   fp.one = 1.0f;
-  fp.d[0] = FinDir{keys1, c1, soa2, dist1, idx1, n1, tiles_of(n2), (long long)b * n1};
-  if (ndir == 2) fp.d[1] = FinDir{keys2, c2, soa1, dist2, idx2, n2, tiles_of(n1), (long long)b * n2};
-  {
-    const long long total = fp.d[0].count > fp.d[1].count ? fp.d[0].count : fp.d[1].count;
-    long long blocks = (total + 255) / 256;
-    if (blocks > (long long)di.sms * 16) blocks = (long long)di.sms * 16;
-    nnd_finalize_kernel<kTT, kChunk><<<(unsigned)blocks, 256, 0, st>>>(fp);
-    ++g_launches;
-    if (ev) cudaEventRecord(ev[3], st);
-  }
+  fp.d[0] = FinDir{keys, q, soat, dist, idx, nq, tiles_of(nt), 0, nq, (long long)b * nq};
+  nnd_finalize_kernel<kTT, kChunk><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
+  ++g_launches;
+  if (ev) cudaEventRecord(ev[3], st);
   return check_last(cudaGetLastError());
 }
 
@@ -705,8 +782,20 @@ const char* nnd_error_string(int code) {
 
 size_t nnd_workspace_bytes(int b, int n, int m) {
   if (b <= 0 || n <= 0 || m <= 0) return 256;
-  return soa_bytes(b, n) + soa_bytes(b, m) + key_bytes(b, n) + key_bytes_padded(b, m);
+  return nnd_rows_workspace_bytes(b, n, m) + colkey_bytes(b, m);
 }
+
+size_t nnd_rows_workspace_bytes(int b, int n, int m) {
+  if (b <= 0 || n <= 0 || m <= 0) return 256;
+  return soa_bytes(b, n) + soa_bytes(b, m) + key_bytes(b, n) + filter_bytes(b, m);
+}
+
+size_t nnd_colkeys_count(int b, int m) {
+  if (b <= 0 || m <= 0) return 0;
+  return colkey_count(b, m);
+}
+
+int nnd_row_group(void) { return kQPT; }
 
 size_t nnd_query_workspace_bytes(int b, int nq, int nt) {
   if (b <= 0 || nq <= 0 || nt <= 0) return 256;
@@ -715,17 +804,46 @@ size_t nnd_query_workspace_bytes(int b, int nq, int nt) {
 
 int nnd_last_launch_count(void) { return g_launches; }
 
+static bool sizes_ok(int b, int n, int m) {
+  if (b < 0 || n < 0 || m < 0) return false;
+  return (long long)b * n <= 0x7fffffffLL / 3 * 256 && (long long)b * m <= 0x7fffffffLL / 3 * 256;
+}
+
 int nnd_forward_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int m, float* dist1, float* dist2,
                          int32_t* idx1, int32_t* idx2, void* workspace, size_t workspace_bytes, void* stream) {
   g_launches = 0;
-  if (b < 0 || n < 0 || m < 0) return NND_EINVAL;
-  if ((long long)b * n > 0x7fffffffLL / 3 * 256 || (long long)b * m > 0x7fffffffLL / 3 * 256) return NND_EINVAL;
+  if (!sizes_ok(b, n, m)) return NND_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   if (b == 0 || (n == 0 && m == 0)) return 0;
   if (n == 0) return zero_outputs(dist2, idx2, (long long)b * m, st);  // my_lib.cpp:9-10,21-22 with an empty inner loop
   if (m == 0) return zero_outputs(dist1, idx1, (long long)b * n, st);
   if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2 || !workspace) return NND_EINVAL;
-  return forward_impl(xyz1, n, xyz2, m, b, 2, dist1, idx1, dist2, idx2, workspace, workspace_bytes, st);
+  if (workspace_bytes < nnd_workspace_bytes(b, n, m)) return NND_EWORKSPACE;
+  const size_t rows_bytes = nnd_rows_workspace_bytes(b, n, m);
+  unsigned long long* colkeys = (unsigned long long*)((char*)workspace + rows_bytes);
+  int rc = forward_rows_impl(xyz1, n, xyz2, m, b, 0, n, dist1, idx1, colkeys, workspace, rows_bytes, st);
+  if (rc) return rc;
+  return finalize_cols_impl(xyz1, n, xyz2, m, b, colkeys, dist2, idx2, st);
+}
+
+int nnd_forward_rows_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int m, int row_lo, int row_hi,
+                              float* dist1, int32_t* idx1, unsigned long long* colkeys, void* workspace,
+                              size_t workspace_bytes, void* stream) {
+  g_launches = 0;
+  if (!sizes_ok(b, n, m) || b == 0 || n == 0 || m == 0) return NND_EINVAL;
+  if (row_lo < 0 || row_hi < row_lo || row_hi > n) return NND_EINVAL;
+  if (row_lo % kQPT != 0 || (row_hi % kQPT != 0 && row_hi != n)) return NND_EINVAL;  // whole row groups only
+  if (!xyz1 || !xyz2 || !dist1 || !idx1 || !colkeys || !workspace) return NND_EINVAL;
+  return forward_rows_impl(xyz1, n, xyz2, m, b, row_lo, row_hi, dist1, idx1, colkeys, workspace, workspace_bytes,
+                           (cudaStream_t)stream);
+}
+
+int nnd_finalize_cols_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int m,
+                               const unsigned long long* colkeys, float* dist2, int32_t* idx2, void* stream) {
+  g_launches = 0;
+  if (!sizes_ok(b, n, m) || b == 0 || n == 0 || m == 0) return NND_EINVAL;
+  if (!xyz1 || !xyz2 || !colkeys || !dist2 || !idx2) return NND_EINVAL;
+  return finalize_cols_impl(xyz1, n, xyz2, m, b, colkeys, dist2, idx2, (cudaStream_t)stream);
 }
 
 int nnd_profile_enable(int on) {
@@ -768,7 +886,7 @@ int nnd_query_cuda_f32(const float* query, const float* target, int b, int nq, i
   if (b == 0 || nq == 0) return 0;
   if (nt == 0) return zero_outputs(dist, idx, (long long)b * nq, st);
   if (!query || !target || !dist || !idx || !workspace) return NND_EINVAL;
-  return forward_impl(query, nq, target, nt, b, 1, dist, idx, nullptr, nullptr, workspace, workspace_bytes, st);
+  return query_impl(query, nq, target, nt, b, dist, idx, workspace, workspace_bytes, st);
 }
 
 int nnd_backward_term_cuda_f32(const float* query, const float* target, const float* graddist, const int32_t* idx,

@@ -7,22 +7,27 @@
 //   row minima give dist1/idx1 and the column minima give dist2/idx2.
 //
 // Rows (xyz1 points, in registers) are handled exactly like nnd_scan_kernel: per-chunk minimum, first chunk wins,
-// key = (dist_bits << 32 | chunk_base), resolved by nnd_finalize_kernel.
-// Columns (xyz2 points, streamed through shared memory): every thread owns QPT CONSECUTIVE rows j = g*QPT .. g*QPT+QPT-1
-// ("group" g), so a smaller g means smaller row indices.  Per target the thread reduces its QPT distances to one
-// value c (3-input FMNMX tree).  The current global column key of every target travels with the tile (second TMA
-// copy) as a snapshot; only when some lane's c is <= the snapshot distance (rare once a target has seen a few
-// thousand rows) the warp takes the slow path: CREDUX.MIN over the lanes, lowest lane holding the minimum (=
-// lowest group) issues atomicMin(key = dist_bits << 32 | g) on the global key and on the shared-memory snapshot.
-// A stale snapshot is only ever too large, so no improvement or tie is missed.  nnd_finalize_cols_kernel resolves
-// the lowest row inside the winning group.
+// key = (dist_bits << 32 | chunk_base), resolved by nnd_finalize_kernel.  A launch covers the row range
+// [row_lo, row_hi) of every batch element (the multi-GPU path gives each rank one range; row_lo % QPT == 0).
+// Columns (xyz2 points, streamed through shared memory): every thread owns QPT CONSECUTIVE rows
+// j = g*QPT .. g*QPT+QPT-1 ("group" g, numbered globally), so a smaller g means smaller row indices.  Per target the
+// thread reduces its QPT distances to one value c (3-input FMNMX tree).  A 32-bit FILTER array cdist[k] (an upper
+// bound of the current column minimum's bit pattern) travels with the tile (second TMA copy); only when some lane's
+// c is <= the filter value (rare once a target has seen a few thousand rows) the warp takes the slow path:
+// CREDUX.MIN over the lanes, lowest lane holding the minimum (= lowest group) issues atomicMin(key = dist_bits << 32
+// | g) on the global 64-bit column key and lowers the filter (global and the shared-memory copy).  A stale filter is
+// only ever too large, so no improvement or tie is missed.  Column keys of different launches (ranks) merge by a
+// plain integer MIN (all keys are < 2^63), and nnd_finalize_cols_kernel resolves the lowest row inside the winning
+// group.
 
 struct SymParams {
   const float* qsoa;          // xyz1 as SoA tiles [b][qtiles][3][TT]  (rows)
   const float* tsoa;          // xyz2 as SoA tiles [b][ttiles][3][TT]  (columns)
-  unsigned long long* rkeys;  // [b][n]            (dist_bits << 32 | chunk_base)   pre-set to ~0
-  unsigned long long* ckeys;  // [b][ttiles * TT]  (dist_bits << 32 | row group)    pre-set to ~0
+  unsigned long long* rkeys;  // [b][n]            (dist_bits << 32 | chunk_base)   pre-set to kKeyInit
+  unsigned long long* ckeys;  // [b][ttiles * TT]  (dist_bits << 32 | row group)    pre-set to kKeyInit
+  unsigned* cdist;            // [b][ttiles * TT]  filter: >= dist_bits of ckeys    pre-set to 0xffffffff
   int n, m;
+  int row_lo, row_hi;  // rows of every batch element this launch covers; row_lo % QPT == 0
   int qtiles, ttiles, qblocks;
   long long total_units;  // b * qblocks * ttiles
   float one;
@@ -42,7 +47,7 @@ struct FinColParams {
 template <int TT>
 struct __align__(128) SymStage {
   float xyz[3 * TT];
-  unsigned long long snap[TT];
+  unsigned filt[TT];
 };
 
 template <int THREADS, int QPT, int TT, int C, int STAGES, int MINB>
@@ -50,7 +55,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
   static_assert(TT % C == 0 && C % 4 == 0 && QPT % 2 == 0 && TT % QPT == 0, "tile/chunk shape");
   constexpr int QB = THREADS * QPT;
   constexpr uint32_t XYZ_BYTES = 3 * TT * sizeof(float);
-  constexpr uint32_t SNAP_BYTES = TT * sizeof(unsigned long long);
+  constexpr uint32_t FILT_BYTES = TT * sizeof(unsigned);
   constexpr unsigned FULL = 0xffffffffu;
   extern __shared__ __align__(128) unsigned char sym_smem[];
   SymStage<TT>* stages = reinterpret_cast<SymStage<TT>*>(sym_smem);
@@ -74,9 +79,9 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
     const int tile = (int)(pu - qb * p.ttiles);
     const long long batch = qb / p.qblocks;
     const long long t = batch * p.ttiles + tile;
-    mbar_expect_tx(&full[stage], XYZ_BYTES + SNAP_BYTES);
+    mbar_expect_tx(&full[stage], XYZ_BYTES + FILT_BYTES);
     tma_load_1d(stages[stage].xyz, p.tsoa + t * (3 * TT), XYZ_BYTES, &full[stage]);
-    tma_load_1d(stages[stage].snap, p.ckeys + t * TT, SNAP_BYTES, &full[stage]);
+    tma_load_1d(stages[stage].filt, p.cdist + t * TT, FILT_BYTES, &full[stage]);
     ++pu;
   };
   if (tid == 0) {
@@ -102,12 +107,12 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
     uint64_t nqx[QPT], nqy[QPT], nqz[QPT];
     float best[QPT];
     int bchunk[QPT];
-    const unsigned group = (unsigned)(qblock * THREADS + tid);  // row group id inside this batch element
+    const unsigned group = (unsigned)(p.row_lo / QPT + qblock * THREADS + tid);  // global row group id
     const float* qbase = p.qsoa + (long long)batch * p.qtiles * (3 * TT);
 #pragma unroll
     for (int q = 0; q < QPT; ++q) {
-      int j = qblock * QB + tid * QPT + q;
-      j = j < p.n ? j : p.n - 1;
+      int j = p.row_lo + qblock * QB + tid * QPT + q;
+      j = j < p.row_hi ? j : p.row_hi - 1;  // a repeated row sits in a higher group: it never wins a tie
       const int qt = j / TT, qo = j - qt * TT;
       const float* s = qbase + (long long)qt * (3 * TT) + qo;
       const float x = -s[0], y = -s[TT], z = -s[2 * TT];
@@ -118,6 +123,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
       bchunk[q] = 0;
     }
     unsigned long long* ckeys = p.ckeys + (long long)batch * p.ttiles * TT;
+    unsigned* cdist = p.cdist + (long long)batch * p.ttiles * TT;
 
     for (int tile = tile0; tile < tile0 + seg_tiles; ++tile) {
       const int stage = cnt % STAGES;
@@ -125,7 +131,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
       const float* sx = stages[stage].xyz;
       const float* sy = sx + TT;
       const float* sz = sx + 2 * TT;
-      unsigned long long* snap = stages[stage].snap;
+      unsigned* filt = stages[stage].filt;
       const int valid = min(TT, p.m - tile * TT);
       const int nchunks = (valid + C - 1) / C;
 
@@ -135,11 +141,15 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
         const ulonglong2* cz = reinterpret_cast<const ulonglong2*>(sz + ch * C);
         float cm[QPT];
 #pragma unroll
-        for (int q = 0; q < QPT; ++q) cm[q] = INF;
+        for (int q = 0; q < QPT; ++q) cm[q] = NND_MIN_VARIANT == 5 ? -INF : INF;
 #pragma unroll
         for (int s4 = 0; s4 < C / 4; ++s4) {
           const ulonglong2 X = cx[s4], Y = cy[s4], Z = cz[s4];
+#if NND_MIN_VARIANT == 4 || NND_MIN_VARIANT == 5
+          float c0 = -INF, c1 = -INF, c2 = -INF, c3 = -INF;  // NEGATED column minima over this thread's rows
+#else
           float c0 = INF, c1 = INF, c2 = INF, c3 = INF;  // column minima over this thread's rows
+#endif
 #pragma unroll
           for (int q = 0; q < QPT; q += 2) {
             float a0, a1, b0, b1, e0, e1, f0, f1;
@@ -147,6 +157,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
             upk2(sqdist2(X.y, Y.y, Z.y, nqx[q], nqy[q], nqz[q], one), b0, b1);
             upk2(sqdist2(X.x, Y.x, Z.x, nqx[q + 1], nqy[q + 1], nqz[q + 1], one), e0, e1);
             upk2(sqdist2(X.y, Y.y, Z.y, nqx[q + 1], nqy[q + 1], nqz[q + 1], one), f0, f1);
+#if NND_MIN_VARIANT == 0
             cm[q] = fmin3(cm[q], a0, a1);
             cm[q] = fmin3(cm[q], b0, b1);
             cm[q + 1] = fmin3(cm[q + 1], e0, e1);
@@ -155,28 +166,86 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
             c1 = fmin3(c1, a1, e1);
             c2 = fmin3(c2, b0, f0);
             c3 = fmin3(c3, b1, f1);
+#elif NND_MIN_VARIANT == 1
+            // 2-input minima only (FMNMX): alternate the plain and the xorsign.abs flavour so that ptxas
+            // cannot merge two of them into one FMNMX3
+            cm[q] = fminf(cm[q], fmin_xs(fmin_xs(a0, a1), fmin_xs(b0, b1)));
+            cm[q + 1] = fminf(cm[q + 1], fmin_xs(fmin_xs(e0, e1), fmin_xs(f0, f1)));
+            c0 = fminf(c0, fmin_xs(a0, e0));
+            c1 = fminf(c1, fmin_xs(a1, e1));
+            c2 = fminf(c2, fmin_xs(b0, f0));
+            c3 = fminf(c3, fmin_xs(b1, f1));
+#elif NND_MIN_VARIANT == 3
+            // integer 3-input minima (VIMNMX3): d >= +0 so the int order of the bits is the float order
+            cm[q] = imin3f(cm[q], a0, a1);
+            cm[q] = imin3f(cm[q], b0, b1);
+            cm[q + 1] = imin3f(cm[q + 1], e0, e1);
+            cm[q + 1] = imin3f(cm[q + 1], f0, f1);
+            c0 = imin3f(c0, a0, e0);
+            c1 = imin3f(c1, a1, e1);
+            c2 = imin3f(c2, b0, f0);
+            c3 = imin3f(c3, b1, f1);
+#elif NND_MIN_VARIANT == 4
+            // rows with FMNMX3; columns keep the NEGATED running minimum: nc = max(nc, -min(a, e))
+            cm[q] = fmin3(cm[q], a0, a1);
+            cm[q] = fmin3(cm[q], b0, b1);
+            cm[q + 1] = fmin3(cm[q + 1], e0, e1);
+            cm[q + 1] = fmin3(cm[q + 1], f0, f1);
+            c0 = fmaxf(c0, -fminf(a0, e0));
+            c1 = fmaxf(c1, -fminf(a1, e1));
+            c2 = fmaxf(c2, -fminf(b0, f0));
+            c3 = fmaxf(c3, -fminf(b1, f1));
+#elif NND_MIN_VARIANT == 5
+            // rows: negated running chunk minimum, one FMNMX3 + two FMNMX per 4 values; columns as variant 4
+            cm[q] = fmaxf(cm[q], -fmin3(a0, a1, fminf(b0, b1)));
+            cm[q + 1] = fmaxf(cm[q + 1], -fmin3(e0, e1, fminf(f0, f1)));
+            c0 = fmaxf(c0, -fminf(a0, e0));
+            c1 = fmaxf(c1, -fminf(a1, e1));
+            c2 = fmaxf(c2, -fminf(b0, f0));
+            c3 = fmaxf(c3, -fminf(b1, f1));
+#elif NND_MIN_VARIANT == 2
+            // half and half: rows with FMNMX3, columns with 2-input FMNMX
+            cm[q] = fmin3(cm[q], a0, a1);
+            cm[q] = fmin3(cm[q], b0, b1);
+            cm[q + 1] = fmin3(cm[q + 1], e0, e1);
+            cm[q + 1] = fmin3(cm[q + 1], f0, f1);
+            c0 = fminf(c0, fmin_xs(a0, e0));
+            c1 = fminf(c1, fmin_xs(a1, e1));
+            c2 = fminf(c2, fmin_xs(b0, f0));
+            c3 = fminf(c3, fmin_xs(b1, f1));
+#endif
           }
-          // ---- columns: compare with the snapshot of the global keys (high word = distance bits)
+          // ---- columns: compare with the filter (an upper bound of the column minimum's bit pattern)
           const int koff = ch * C + 4 * s4;
-          const ulonglong2 K01 = *reinterpret_cast<const ulonglong2*>(snap + koff);
-          const ulonglong2 K23 = *reinterpret_cast<const ulonglong2*>(snap + koff + 2);
-          const unsigned h0 = (unsigned)(K01.x >> 32), h1 = (unsigned)(K01.y >> 32);
-          const unsigned h2 = (unsigned)(K23.x >> 32), h3 = (unsigned)(K23.y >> 32);
+          const uint4 H = *reinterpret_cast<const uint4*>(filt + koff);
+          const unsigned h0 = H.x, h1 = H.y, h2 = H.z, h3 = H.w;
+#if NND_MIN_VARIANT == 4 || NND_MIN_VARIANT == 5
+          const unsigned u0 = __float_as_uint(-c0), u1 = __float_as_uint(-c1);
+          const unsigned u2 = __float_as_uint(-c2), u3 = __float_as_uint(-c3);
+#else
           const unsigned u0 = __float_as_uint(c0), u1 = __float_as_uint(c1);
           const unsigned u2 = __float_as_uint(c2), u3 = __float_as_uint(c3);
+#endif
           const bool ev = (u0 <= h0) | (u1 <= h1) | (u2 <= h2) | (u3 <= h3);
           if (__any_sync(FULL, ev)) {
             const unsigned uu[4] = {u0, u1, u2, u3};
             const unsigned hh[4] = {h0, h1, h2, h3};
 #pragma unroll
             for (int t = 0; t < 4; ++t) {
-              const unsigned mn = __reduce_min_sync(FULL, uu[t]);
-              if (mn <= hh[t]) {  // warp-uniform
+              // The lanes of a warp need not be converged when they load the filter (independent thread
+              // scheduling, e.g. after the mbarrier spin), so hh[t] may differ between lanes while another warp
+              // lowers the filter.  Every decision that guards a collective must therefore itself come from a
+              // collective: the ballot is identical in all lanes.
+              if (__ballot_sync(FULL, uu[t] <= hh[t]) != 0u) {
+                // The lowest value over ALL lanes is a true distance of its group, so posting it is always
+                // valid, and it is <= the value of every lane that passed its filter: nothing is missed.
+                const unsigned mn = __reduce_min_sync(FULL, uu[t]);
                 const unsigned holders = __ballot_sync(FULL, uu[t] == mn);
                 if (lane == (unsigned)(__ffs(holders) - 1)) {  // lowest lane = lowest row group
                   const unsigned long long key = ((unsigned long long)mn << 32) | group;
                   atomicMin(ckeys + (long long)tile * TT + koff + t, key);
-                  atomicMin(snap + koff + t, key);
+                  atomicMin(cdist + (long long)tile * TT + koff + t, mn);
+                  atomicMin(filt + koff + t, mn);
                 }
               }
             }
@@ -185,11 +254,11 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
         const int cbase = tile * TT + ch * C;
 #pragma unroll
         for (int q = 0; q < QPT; ++q) {
+          if (NND_MIN_VARIANT == 5) cm[q] = -cm[q];
           if (cm[q] < best[q]) bchunk[q] = cbase;
           best[q] = fminf(best[q], cm[q]);
         }
       }
-
       __syncthreads();
       if (tid == 0 && pu < u_end) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -201,8 +270,8 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
     unsigned long long* rkeys = p.rkeys + (long long)batch * p.n;
 #pragma unroll
     for (int q = 0; q < QPT; ++q) {
-      const int j = qblock * QB + tid * QPT + q;
-      if (j < p.n) {
+      const int j = p.row_lo + qblock * QB + tid * QPT + q;
+      if (j < p.row_hi) {
         const unsigned long long key =
             ((unsigned long long)__float_as_uint(best[q]) << 32) | (unsigned long long)(unsigned)bchunk[q];
         atomicMin(rkeys + j, key);

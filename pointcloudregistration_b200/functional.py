@@ -64,6 +64,60 @@ def nnd_forward_raw(xyz1: torch.Tensor, xyz2: torch.Tensor):
     return dist1, dist2, idx1, idx2
 
 
+def row_group() -> int:
+    """Row ranges handed to nnd_forward_rows_raw must start (and, unless they end at N, end) on a multiple of this."""
+    return int(_cabi.load().nnd_row_group())
+
+
+def nnd_forward_rows_raw(xyz1: torch.Tensor, xyz2: torch.Tensor, row_lo: int, row_hi: int):
+    """Symmetric forward over rows [row_lo, row_hi) of xyz1 (include/nnd_b200.h: nnd_forward_rows_cuda_f32).
+
+    Returns (dist1 [B, rows] f32, idx1 [B, rows] int32, colkeys [B * nnd_colkeys_count(1, M)] int64): the rows'
+    final results and the packed per-column partial results, to be merged across ranks with an integer MIN and
+    resolved by nnd_finalize_cols_raw."""
+    _check_clouds(xyz1, xyz2)
+    lib = _cabi.load()
+    xyz1 = xyz1.contiguous()
+    xyz2 = xyz2.contiguous()
+    b, n, _ = xyz1.shape
+    m = xyz2.size(1)
+    dev = xyz1.device
+    if b == 0 or n == 0 or m == 0:
+        raise ValueError("nnd_forward_rows_raw needs non-empty clouds")
+    dist1 = torch.empty(b, n, dtype=torch.float32, device=dev)
+    idx1 = torch.empty(b, n, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        colkeys = torch.empty(lib.nnd_colkeys_count(b, m), dtype=torch.int64, device=dev)
+        ws = _workspace(lib.nnd_rows_workspace_bytes(b, n, m), dev)
+        rc = lib.nnd_forward_rows_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), b, n, m, int(row_lo), int(row_hi),
+                                           dist1.data_ptr(), idx1.data_ptr(), colkeys.data_ptr(), ws.data_ptr(),
+                                           ws.numel(), _stream_ptr(dev))
+    _cabi.check(rc, "nnd_forward_rows_cuda_f32")
+    return dist1[:, row_lo:row_hi], idx1[:, row_lo:row_hi], colkeys
+
+
+def nnd_finalize_cols_raw(xyz1: torch.Tensor, xyz2: torch.Tensor, colkeys: torch.Tensor):
+    """dist2 [B,M] f32, idx2 [B,M] int32 from (merged) column keys."""
+    _check_clouds(xyz1, xyz2)
+    lib = _cabi.load()
+    xyz1 = xyz1.contiguous()
+    xyz2 = xyz2.contiguous()
+    b, n, _ = xyz1.shape
+    m = xyz2.size(1)
+    dev = xyz1.device
+    if colkeys.dtype != torch.int64 or not colkeys.is_contiguous() or colkeys.device != dev:
+        raise TypeError("colkeys must be the contiguous int64 tensor nnd_forward_rows_raw returned")
+    if colkeys.numel() != lib.nnd_colkeys_count(b, m):
+        raise ValueError("colkeys has the wrong length for these clouds")
+    dist2 = torch.empty(b, m, dtype=torch.float32, device=dev)
+    idx2 = torch.empty(b, m, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.nnd_finalize_cols_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), b, n, m, colkeys.data_ptr(),
+                                            dist2.data_ptr(), idx2.data_ptr(), _stream_ptr(dev))
+    _cabi.check(rc, "nnd_finalize_cols_cuda_f32")
+    return dist2, idx2
+
+
 def nnd_query_raw(query: torch.Tensor, target: torch.Tensor):
     """One direction: for every query point its nearest target. dist[B,Nq] f32, idx[B,Nq] int32."""
     _check_clouds(query, target)

@@ -1,19 +1,25 @@
-"""Query-sharded nnd across the GPUs of one box (one process per GPU, torch.distributed / NCCL).
+"""Row-sharded nnd across the GPUs of one box (one process per GPU, torch.distributed / NCCL).
 
 The reference has no multi-device path; this is new design for BASELINE.json
-configs[3].  Every query row is independent, so rank r owns rows [r*N/G, (r+1)*N/G) of cloud 1
-AND rows [r*M/G, (r+1)*M/G) of cloud 2 as *queries*; both clouds are needed in full on every
-rank as *targets* (12 MB per million points), so they are broadcast over NVLink.  Exchange steps:
+configs[3].  The forward evaluates every (xyz1[j], xyz2[k]) distance ONCE and serves both
+directions from it (csrc/nnd_sym.cuh), so the unit of sharding is a range of xyz1 ROWS: rank r
+owns rows [lo1_r, hi1_r) (boundaries on multiples of the kernel's row group).  Both clouds are
+needed in full on every rank (12 MB per million points), so they are broadcast over NVLink.
 
     forward : broadcast(xyz1), broadcast(xyz2)            [optional: caller may already hold them]
-              all_gather(dist/idx shards)                 [optional: gather=False keeps shards]
-    backward: all_reduce(SUM) of gradxyz1, gradxyz2       (scatter terms land anywhere in the other cloud)
+              rows kernel  -> dist1/idx1 of the own rows (final) + per-column partial keys
+              all_reduce(MIN, int64) of the column keys   <- the one real exchange step (8 B / point)
+              column finalize -> dist2/idx2, replicated
+              all_gather(dist1/idx1 row shards)           [optional: gather=False keeps shards]
+    backward: term 1 over the own xyz1 rows, term 2 over the own slice of xyz2 rows,
+              all_reduce(SUM) of gradxyz1, gradxyz2       (scatter terms land anywhere in the other cloud)
 
-Forward results are bit-identical for any G (pure per-row function).  Gradients differ from the
-1-GPU result only by fp32 summation order (within the 1e-5 contract).
+Forward results are bit-identical for any G: row results are a pure per-row function, and a column
+key (dist_bits << 32 | row_group) is an order-independent integer minimum.  Gradients differ from
+the 1-GPU result only by fp32 summation order (within the 1e-5 contract).
 
-The collectives are plain NCCL calls: at N=M=1M they move ~60 MB per step against >= 50 ms of
-compute per GPU, i.e. < 0.2 % of the step, so a fused compute+collective kernel has nothing to
+The collectives are plain NCCL calls: at N=M=1M they move ~60 MB per step against >= 35 ms of
+compute per GPU at G=8, i.e. ~1 % of the step, so a fused compute+collective kernel has nothing to
 overlap (numbers in DESIGN.md).
 
 `compute` is the per-rank engine.  The product default is the CUDA C ABI; the CPU `gloo` tests
@@ -28,9 +34,14 @@ import torch.distributed as dist
 from torch.autograd import Function
 
 
-def shard_range(n: int, world: int, rank: int) -> tuple[int, int]:
-    """Contiguous balanced split of n rows: sizes differ by at most one."""
-    return (n * rank) // world, (n * (rank + 1)) // world
+def shard_range(n: int, world: int, rank: int, align: int = 1) -> tuple[int, int]:
+    """Contiguous balanced split of n rows; interior boundaries are rounded down to multiples of `align`."""
+    def cut(r: int) -> int:
+        if r >= world:
+            return n
+        return (n * r) // world // align * align
+
+    return cut(rank), cut(rank + 1)
 
 
 @dataclass
@@ -47,10 +58,23 @@ class CudaCompute:
     """Per-rank engine on the C ABI (include/nnd_b200.h).  No fallback."""
 
     @staticmethod
-    def query(q: torch.Tensor, t: torch.Tensor):
-        from .functional import nnd_query_raw
+    def row_group() -> int:
+        from .functional import row_group
 
-        return nnd_query_raw(q, t)
+        return row_group()
+
+    @staticmethod
+    def rows(xyz1: torch.Tensor, xyz2: torch.Tensor, lo: int, hi: int):
+        """(dist1 [B,hi-lo], idx1 [B,hi-lo], colkeys int64) for rows [lo, hi) of xyz1 against all of xyz2."""
+        from .functional import nnd_forward_rows_raw
+
+        return nnd_forward_rows_raw(xyz1, xyz2, lo, hi)
+
+    @staticmethod
+    def finalize_cols(xyz1: torch.Tensor, xyz2: torch.Tensor, colkeys: torch.Tensor):
+        from .functional import nnd_finalize_cols_raw
+
+        return nnd_finalize_cols_raw(xyz1, xyz2, colkeys)
 
     @staticmethod
     def backward_term(q, t, gd, idx, grad_q, grad_t) -> None:
@@ -75,39 +99,47 @@ def _world(group):
     return dist.get_rank(group), dist.get_world_size(group)
 
 
-def _gather_rows(shard: torch.Tensor, n: int, world: int, group) -> torch.Tensor:
-    """all_gather of [B, rows_r] shards with rows_r = shard_range sizes (differ by <= 1) -> [B, n]."""
+def _gather_rows(shard: torch.Tensor, n: int, world: int, group, align: int) -> torch.Tensor:
+    """all_gather of [B, rows_r] shards (rows_r = shard_range sizes) -> [B, n]."""
     if world == 1:
-        return shard
+        return shard.contiguous()
     b = shard.size(0)
-    longest = max(shard_range(n, world, r)[1] - shard_range(n, world, r)[0] for r in range(world))
+    ranges = [shard_range(n, world, r, align) for r in range(world)]
+    longest = max(hi - lo for lo, hi in ranges)
     padded = shard.new_zeros(b, longest)
     padded[:, :shard.size(1)] = shard
     bufs = [torch.empty_like(padded) for _ in range(world)]
     dist.all_gather(bufs, padded, group=group)
-    parts = []
-    for r in range(world):
-        lo, hi = shard_range(n, world, r)
-        parts.append(bufs[r][:, :hi - lo])
-    return torch.cat(parts, dim=1)
+    return torch.cat([bufs[r][:, :hi - lo] for r, (lo, hi) in enumerate(ranges)], dim=1)
 
 
 def sharded_forward(xyz1, xyz2, group=None, src=None, gather=True, compute=CudaCompute):
     """Returns (dist1, dist2, idx1, idx2, info).  With gather=True the four tensors are full-size and
-    identical on every rank; otherwise they are this rank's row shards."""
+    identical on every rank; otherwise they are this rank's row shards ([lo1,hi1) of cloud 1, [lo2,hi2) of
+    cloud 2)."""
     rank, world = _world(group)
     if src is not None and world > 1:
         dist.broadcast(xyz1, src=src, group=group)
         dist.broadcast(xyz2, src=src, group=group)
     n, m = xyz1.size(1), xyz2.size(1)
-    lo1, hi1 = shard_range(n, world, rank)
+    align = compute.row_group()
+    lo1, hi1 = shard_range(n, world, rank, align)
     lo2, hi2 = shard_range(m, world, rank)
     info = ShardInfo(rank, world, lo1, hi1, lo2, hi2)
-    d1, i1 = compute.query(xyz1[:, lo1:hi1].contiguous(), xyz2)
-    d2, i2 = compute.query(xyz2[:, lo2:hi2].contiguous(), xyz1)
+    if xyz1.size(0) == 0 or n == 0 or m == 0:  # my_lib.cpp:9-10,21-22: empty inner loop -> zeros
+        z = lambda cols: (xyz1.new_zeros(xyz1.size(0), cols), torch.zeros(xyz1.size(0), cols, dtype=torch.int32,  # noqa: E731
+                                                                          device=xyz1.device))
+        (d1, i1), (d2, i2) = z(n if gather else hi1 - lo1), z(m if gather else hi2 - lo2)
+        return d1, d2, i1, i2, info
+    d1, i1, colkeys = compute.rows(xyz1, xyz2, lo1, hi1)
+    if world > 1:
+        dist.all_reduce(colkeys, op=dist.ReduceOp.MIN, group=group)
+    d2, i2 = compute.finalize_cols(xyz1, xyz2, colkeys)
     if gather:
-        d1, i1 = _gather_rows(d1, n, world, group), _gather_rows(i1, n, world, group)
-        d2, i2 = _gather_rows(d2, m, world, group), _gather_rows(i2, m, world, group)
+        d1, i1 = _gather_rows(d1, n, world, group, align), _gather_rows(i1, n, world, group, align)
+    else:
+        d1, i1 = d1.contiguous(), i1.contiguous()
+        d2, i2 = d2[:, lo2:hi2].contiguous(), i2[:, lo2:hi2].contiguous()
     return d1, d2, i1, i2, info
 
 

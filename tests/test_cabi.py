@@ -19,7 +19,7 @@ def declared_symbols():
 def test_header_declares_the_expected_entry_points():
     syms = declared_symbols()
     for s in ("nnd_forward_cuda_f32", "nnd_backward_cuda_f32", "nnd_query_cuda_f32", "nnd_backward_term_cuda_f32",
-              "nnd_workspace_bytes", "nnd_version"):
+              "nnd_workspace_bytes", "nnd_version", "nnd_forward_rows_cuda_f32", "nnd_finalize_cols_cuda_f32"):
         assert s in syms
 
 
@@ -39,10 +39,13 @@ def test_version_and_error_strings(cuda_lib):
 
 
 def test_workspace_size_formula(cuda_lib):
-    # SoA copies (12 B/point, padded to 512-point tiles) + 8 B/point keys for both clouds
+    # SoA copies (12 B/point, padded to 512-point tiles) + 8 B/point keys for both clouds + 4 B/point column filter
     w = cuda_lib.nnd_workspace_bytes(1, 1_000_000, 1_000_000)
-    assert 2 * 1_000_000 * 20 <= w <= 2 * 1_000_000 * 20 + 64 * 1024
+    assert 1_000_000 * 44 <= w <= 1_000_000 * 44 + 64 * 1024
     assert cuda_lib.nnd_workspace_bytes(0, 10, 10) == 256
+    # the row-range entry point keeps the column keys in a caller-owned buffer (they are all-reduced)
+    assert cuda_lib.nnd_rows_workspace_bytes(1, 1_000_000, 1_000_000) + 8 * cuda_lib.nnd_colkeys_count(1, 1_000_000) <= w
+    assert cuda_lib.nnd_colkeys_count(3, 513) == 3 * 1024 and cuda_lib.nnd_row_group() == 8
     assert cuda_lib.nnd_query_workspace_bytes(2, 512, 512) == 2 * (2 * 512 * 12) + 2 * 512 * 8
 
 
@@ -52,6 +55,8 @@ def test_argument_validation_needs_no_gpu(cuda_lib):
     assert cuda_lib.nnd_backward_cuda_f32(None, None, None, None, None, None, 1, -5, 1, None, None, None) == 10001
     # b == 0: nothing to do, success without touching the device
     assert cuda_lib.nnd_forward_cuda_f32(None, None, 0, 4, 4, None, None, None, None, None, 0, None) == 0
+    # row ranges must be whole row groups
+    assert cuda_lib.nnd_forward_rows_cuda_f32(None, None, 1, 64, 64, 3, 64, None, None, None, None, 0, None) == 10001
 
 
 def test_forward_kernel_sass_is_bit_exact_form():
@@ -64,8 +69,8 @@ def test_forward_kernel_sass_is_bit_exact_form():
     except (FileNotFoundError, subprocess.CalledProcessError):
         pytest.skip("cuobjdump not available")
     kernels = re.split(r"Function : ", out.stdout)
-    scan = [k for k in kernels if "nnd_scan_kernel" in k.split("\n", 1)[0]]
-    assert scan, "nnd_scan_kernel not found in the cubin"
+    scan = [k for k in kernels if "nnd_scan_kernel" in k.split("\n", 1)[0] or "nnd_scan_sym_kernel" in k.split("\n", 1)[0]]
+    assert len(scan) == 2, "nnd_scan_kernel / nnd_scan_sym_kernel not found in the cubin"
     for k in scan:
         ops = re.findall(r"^\s+/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", k, flags=re.M)
         n = {name: sum(1 for o in ops if o.split(".")[0] == name) for name in ("FFMA", "FMUL2", "FADD2", "FFMA2", "FMNMX3")}

@@ -17,15 +17,60 @@ sys.path.insert(0, str(ROOT))
 sys.path.insert(0, str(ROOT / "tests"))
 
 
+KEY_INIT = np.int64(0x7fffffffffffffff)
+TT = 512  # column keys are padded to whole 512-point tiles (include/nnd_b200.h: nnd_colkeys_count)
+GROUP = 8
+
+
+def _dense_sqdist(p1, p2):
+    """D[j,k] exactly as my_lib.cpp:12-15 evaluates it for query p1[j], target p2[k] (numpy f32 ops are
+    separately rounded IEEE operations, no FMA)."""
+    d = p2[None, :, :] - p1[:, None, :]
+    sq = d * d
+    return (sq[..., 0] + sq[..., 1]) + sq[..., 2]
+
+
 class OracleCompute:
-    """Test-only engine: same interface as sharded.CudaCompute, backed by oracle/ (CPU)."""
+    """Test-only engine: same interface as sharded.CudaCompute, backed by oracle/ and numpy (CPU)."""
 
     @staticmethod
-    def query(q, t):
+    def row_group():
+        return GROUP
+
+    @staticmethod
+    def rows(xyz1, xyz2, lo, hi):
         import oracle
 
-        d, i = oracle.query(q.numpy(), t.numpy())
-        return torch.from_numpy(d), torch.from_numpy(i)
+        assert lo % GROUP == 0 and (hi % GROUP == 0 or hi == xyz1.size(1))
+        b, m = xyz1.size(0), xyz2.size(1)
+        per = (m + TT - 1) // TT * TT
+        keys = np.full((b, per), KEY_INIT, np.int64)
+        if hi > lo:
+            d, i = oracle.query(xyz1[:, lo:hi].contiguous().numpy(), xyz2.numpy())
+            for bi in range(b):
+                D = _dense_sqdist(xyz1[bi, lo:hi].numpy(), xyz2[bi].numpy())  # [rows, m]
+                first = D.argmin(axis=0)  # lowest row attaining the column minimum
+                bits = D[first, np.arange(m)].view(np.int32).astype(np.int64)
+                keys[bi, :m] = (bits << 32) | ((first + lo) // GROUP)
+        else:
+            d = np.zeros((b, 0), np.float32)
+            i = np.zeros((b, 0), np.int32)
+        return torch.from_numpy(d), torch.from_numpy(i), torch.from_numpy(keys.reshape(-1))
+
+    @staticmethod
+    def finalize_cols(xyz1, xyz2, colkeys):
+        b, n, m = xyz1.size(0), xyz1.size(1), xyz2.size(1)
+        keys = colkeys.numpy().reshape(b, -1)[:, :m]
+        dist = (keys >> 32).astype(np.int32).view(np.float32)
+        group = (keys & 0xffffffff).astype(np.int64)
+        idx = np.zeros((b, m), np.int32)
+        for bi in range(b):
+            D = _dense_sqdist(xyz1[bi].numpy(), xyz2[bi].numpy())
+            for k in range(m):
+                rows = np.arange(group[bi, k] * GROUP, min(group[bi, k] * GROUP + GROUP, n))
+                hit = rows[D[rows, k] == dist[bi, k]]
+                idx[bi, k] = hit[0]
+        return torch.from_numpy(np.ascontiguousarray(dist)), torch.from_numpy(idx)
 
     @staticmethod
     def backward_term(q, t, gd, idx, grad_q, grad_t):
@@ -73,7 +118,7 @@ def _worker(rank, world, port, b, n, m, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,b,n,m", [(2, 1, 301, 200), (2, 3, 64, 129), (3, 1, 100, 101)])
+@pytest.mark.parametrize("world,b,n,m", [(2, 1, 301, 200), (2, 3, 64, 129), (3, 1, 100, 101), (3, 2, 10, 7)])
 def test_sharded_matches_unsharded(world, b, n, m, tmp_path):
     import oracle
     from _util import assert_forward_exact, assert_grad_close
@@ -95,11 +140,13 @@ def test_shard_ranges_cover_and_balance():
 
     for n in (0, 1, 7, 8, 1_000_000, 1_000_003):
         for w in (1, 2, 3, 4, 8):
-            r = [shard_range(n, w, k) for k in range(w)]
-            assert r[0][0] == 0 and r[-1][1] == n
-            assert all(r[k][1] == r[k + 1][0] for k in range(w - 1))
-            sizes = [hi - lo for lo, hi in r]
-            assert max(sizes) - min(sizes) <= 1
+            for align in (1, 8):
+                r = [shard_range(n, w, k, align) for k in range(w)]
+                assert r[0][0] == 0 and r[-1][1] == n
+                assert all(r[k][1] == r[k + 1][0] for k in range(w - 1))
+                assert all(lo % align == 0 for lo, _ in r)
+                sizes = [hi - lo for lo, hi in r]
+                assert min(sizes) >= 0 and max(sizes) - min(sizes) <= (1 if align == 1 else 2 * align)
 
 
 def test_single_process_without_process_group():

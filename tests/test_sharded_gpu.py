@@ -34,6 +34,47 @@ def test_world1_cuda_engine_matches_oracle(cuda_lib, device):
     assert_grad_close((a.grad.cpu().numpy(), c.grad.cpu().numpy()), wg)
 
 
+@pytest.mark.parametrize("kind,b,n,m,cuts", [
+    ("crosscopy", 1, 5000, 4100, (0, 2048, 5000)),
+    ("lattice", 2, 3001, 2500, (0, 8, 1000, 1000, 3001)),   # includes an empty range and a one-group range
+    ("identical", 1, 4096, 4096, (0, 4088, 4096)),
+    ("duplicates", 3, 700, 1300, (0, 696, 700)),
+])
+def test_row_ranges_merge_to_the_unsharded_result(cuda_lib, device, kind, b, n, m, cuts):
+    """nnd_forward_rows over disjoint row ranges + integer MIN of the column keys + column finalize
+    == the oracle, bit for bit (what the multi-GPU path does, on one GPU)."""
+    import oracle
+    from _util import assert_forward_exact
+    from pointcloudregistration_b200 import functional as F
+    from pointcloudregistration_b200 import synthetic
+
+    x1, x2 = synthetic.make_pair(kind, b, n, m, 72)
+    a, c = x1.to(device), x2.to(device)
+    d1 = torch.empty(b, n, device=device)
+    i1 = torch.empty(b, n, dtype=torch.int32, device=device)
+    merged = None
+    for lo, hi in zip(cuts[:-1], cuts[1:]):
+        dr, ir, keys = F.nnd_forward_rows_raw(a, c, lo, hi)
+        d1[:, lo:hi], i1[:, lo:hi] = dr, ir
+        merged = keys if merged is None else torch.minimum(merged, keys)
+    d2, i2 = F.nnd_finalize_cols_raw(a, c, merged)
+    want = oracle.forward(x1.numpy(), x2.numpy(), threads=8)
+    assert_forward_exact(tuple(t.cpu().numpy() for t in (d1, d2, i1, i2)), want)
+
+
+def test_row_range_must_be_whole_groups(cuda_lib, device):
+    from pointcloudregistration_b200 import functional as F
+
+    a = torch.rand(1, 100, 3, device=device)
+    c = torch.rand(1, 50, 3, device=device)
+    g = F.row_group()
+    with pytest.raises(RuntimeError):
+        F.nnd_forward_rows_raw(a, c, 1, 100)       # start inside a group
+    with pytest.raises(RuntimeError):
+        F.nnd_forward_rows_raw(a, c, 0, g + 1)     # end inside a group (and not at N)
+    F.nnd_forward_rows_raw(a, c, g, 100)           # ends at N: fine
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
