@@ -50,6 +50,37 @@ struct __align__(128) SymStage {
   unsigned filt[TT];
 };
 
+// Column slow path of nnd_scan_sym_kernel, entered by ALL lanes of a warp when some lane's column minimum passed
+// its filter value.  Deliberately not inlined: it runs for well under 1 % of the 4-target steps, and keeping it out
+// of line keeps its address arithmetic and registers out of the packed-FP32 loop.
+__device__ __noinline__ void sym_column_update(unsigned u0, unsigned u1, unsigned u2, unsigned u3, unsigned h0,
+                                               unsigned h1, unsigned h2, unsigned h3, unsigned lane, unsigned group,
+                                               unsigned long long* ckeys, unsigned* cdist, unsigned* filt,
+                                               int tile_base, int koff) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const unsigned uu[4] = {u0, u1, u2, u3};
+  const unsigned hh[4] = {h0, h1, h2, h3};
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    // The lanes of a warp need not be converged when they load the filter (independent thread scheduling, e.g.
+    // after the mbarrier spin), so hh[t] may differ between lanes while another warp lowers the filter.  Every
+    // decision that guards a collective must therefore itself come from a collective: the ballot is identical in
+    // all lanes.
+    if (__ballot_sync(FULL, uu[t] <= hh[t]) != 0u) {
+      // The lowest value over ALL lanes is a true distance of its group, so posting it is always valid, and it
+      // is <= the value of every lane that passed its filter: nothing is missed.
+      const unsigned mn = __reduce_min_sync(FULL, uu[t]);
+      const unsigned holders = __ballot_sync(FULL, uu[t] == mn);
+      if (lane == (unsigned)(__ffs(holders) - 1)) {  // lowest lane = lowest row group
+        const unsigned long long key = ((unsigned long long)mn << 32) | group;
+        atomicMin(ckeys + (long long)tile_base + koff + t, key);
+        atomicMin(cdist + (long long)tile_base + koff + t, mn);
+        atomicMin(filt + koff + t, mn);
+      }
+    }
+  }
+}
+
 template <int THREADS, int QPT, int TT, int C, int STAGES, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __grid_constant__ SymParams p) {
   static_assert(TT % C == 0 && C % 4 == 0 && QPT % 2 == 0 && TT % QPT == 0, "tile/chunk shape");
@@ -141,15 +172,11 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
         const ulonglong2* cz = reinterpret_cast<const ulonglong2*>(sz + ch * C);
         float cm[QPT];
 #pragma unroll
-        for (int q = 0; q < QPT; ++q) cm[q] = NND_MIN_VARIANT == 5 ? -INF : INF;
+        for (int q = 0; q < QPT; ++q) cm[q] = INF;
 #pragma unroll
         for (int s4 = 0; s4 < C / 4; ++s4) {
           const ulonglong2 X = cx[s4], Y = cy[s4], Z = cz[s4];
-#if NND_MIN_VARIANT == 4 || NND_MIN_VARIANT == 5
-          float c0 = -INF, c1 = -INF, c2 = -INF, c3 = -INF;  // NEGATED column minima over this thread's rows
-#else
           float c0 = INF, c1 = INF, c2 = INF, c3 = INF;  // column minima over this thread's rows
-#endif
 #pragma unroll
           for (int q = 0; q < QPT; q += 2) {
             float a0, a1, b0, b1, e0, e1, f0, f1;
@@ -157,7 +184,6 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
             upk2(sqdist2(X.y, Y.y, Z.y, nqx[q], nqy[q], nqz[q], one), b0, b1);
             upk2(sqdist2(X.x, Y.x, Z.x, nqx[q + 1], nqy[q + 1], nqz[q + 1], one), e0, e1);
             upk2(sqdist2(X.y, Y.y, Z.y, nqx[q + 1], nqy[q + 1], nqz[q + 1], one), f0, f1);
-#if NND_MIN_VARIANT == 0
             cm[q] = fmin3(cm[q], a0, a1);
             cm[q] = fmin3(cm[q], b0, b1);
             cm[q + 1] = fmin3(cm[q + 1], e0, e1);
@@ -166,95 +192,20 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
             c1 = fmin3(c1, a1, e1);
             c2 = fmin3(c2, b0, f0);
             c3 = fmin3(c3, b1, f1);
-#elif NND_MIN_VARIANT == 1
-            // 2-input minima only (FMNMX): alternate the plain and the xorsign.abs flavour so that ptxas
-            // cannot merge two of them into one FMNMX3
-            cm[q] = fminf(cm[q], fmin_xs(fmin_xs(a0, a1), fmin_xs(b0, b1)));
-            cm[q + 1] = fminf(cm[q + 1], fmin_xs(fmin_xs(e0, e1), fmin_xs(f0, f1)));
-            c0 = fminf(c0, fmin_xs(a0, e0));
-            c1 = fminf(c1, fmin_xs(a1, e1));
-            c2 = fminf(c2, fmin_xs(b0, f0));
-            c3 = fminf(c3, fmin_xs(b1, f1));
-#elif NND_MIN_VARIANT == 3
-            // integer 3-input minima (VIMNMX3): d >= +0 so the int order of the bits is the float order
-            cm[q] = imin3f(cm[q], a0, a1);
-            cm[q] = imin3f(cm[q], b0, b1);
-            cm[q + 1] = imin3f(cm[q + 1], e0, e1);
-            cm[q + 1] = imin3f(cm[q + 1], f0, f1);
-            c0 = imin3f(c0, a0, e0);
-            c1 = imin3f(c1, a1, e1);
-            c2 = imin3f(c2, b0, f0);
-            c3 = imin3f(c3, b1, f1);
-#elif NND_MIN_VARIANT == 4
-            // rows with FMNMX3; columns keep the NEGATED running minimum: nc = max(nc, -min(a, e))
-            cm[q] = fmin3(cm[q], a0, a1);
-            cm[q] = fmin3(cm[q], b0, b1);
-            cm[q + 1] = fmin3(cm[q + 1], e0, e1);
-            cm[q + 1] = fmin3(cm[q + 1], f0, f1);
-            c0 = fmaxf(c0, -fminf(a0, e0));
-            c1 = fmaxf(c1, -fminf(a1, e1));
-            c2 = fmaxf(c2, -fminf(b0, f0));
-            c3 = fmaxf(c3, -fminf(b1, f1));
-#elif NND_MIN_VARIANT == 5
-            // rows: negated running chunk minimum, one FMNMX3 + two FMNMX per 4 values; columns as variant 4
-            cm[q] = fmaxf(cm[q], -fmin3(a0, a1, fminf(b0, b1)));
-            cm[q + 1] = fmaxf(cm[q + 1], -fmin3(e0, e1, fminf(f0, f1)));
-            c0 = fmaxf(c0, -fminf(a0, e0));
-            c1 = fmaxf(c1, -fminf(a1, e1));
-            c2 = fmaxf(c2, -fminf(b0, f0));
-            c3 = fmaxf(c3, -fminf(b1, f1));
-#elif NND_MIN_VARIANT == 2
-            // half and half: rows with FMNMX3, columns with 2-input FMNMX
-            cm[q] = fmin3(cm[q], a0, a1);
-            cm[q] = fmin3(cm[q], b0, b1);
-            cm[q + 1] = fmin3(cm[q + 1], e0, e1);
-            cm[q + 1] = fmin3(cm[q + 1], f0, f1);
-            c0 = fminf(c0, fmin_xs(a0, e0));
-            c1 = fminf(c1, fmin_xs(a1, e1));
-            c2 = fminf(c2, fmin_xs(b0, f0));
-            c3 = fminf(c3, fmin_xs(b1, f1));
-#endif
           }
           // ---- columns: compare with the filter (an upper bound of the column minimum's bit pattern)
           const int koff = ch * C + 4 * s4;
           const uint4 H = *reinterpret_cast<const uint4*>(filt + koff);
           const unsigned h0 = H.x, h1 = H.y, h2 = H.z, h3 = H.w;
-#if NND_MIN_VARIANT == 4 || NND_MIN_VARIANT == 5
-          const unsigned u0 = __float_as_uint(-c0), u1 = __float_as_uint(-c1);
-          const unsigned u2 = __float_as_uint(-c2), u3 = __float_as_uint(-c3);
-#else
           const unsigned u0 = __float_as_uint(c0), u1 = __float_as_uint(c1);
           const unsigned u2 = __float_as_uint(c2), u3 = __float_as_uint(c3);
-#endif
           const bool ev = (u0 <= h0) | (u1 <= h1) | (u2 <= h2) | (u3 <= h3);
-          if (__any_sync(FULL, ev)) {
-            const unsigned uu[4] = {u0, u1, u2, u3};
-            const unsigned hh[4] = {h0, h1, h2, h3};
-#pragma unroll
-            for (int t = 0; t < 4; ++t) {
-              // The lanes of a warp need not be converged when they load the filter (independent thread
-              // scheduling, e.g. after the mbarrier spin), so hh[t] may differ between lanes while another warp
-              // lowers the filter.  Every decision that guards a collective must therefore itself come from a
-              // collective: the ballot is identical in all lanes.
-              if (__ballot_sync(FULL, uu[t] <= hh[t]) != 0u) {
-                // The lowest value over ALL lanes is a true distance of its group, so posting it is always
-                // valid, and it is <= the value of every lane that passed its filter: nothing is missed.
-                const unsigned mn = __reduce_min_sync(FULL, uu[t]);
-                const unsigned holders = __ballot_sync(FULL, uu[t] == mn);
-                if (lane == (unsigned)(__ffs(holders) - 1)) {  // lowest lane = lowest row group
-                  const unsigned long long key = ((unsigned long long)mn << 32) | group;
-                  atomicMin(ckeys + (long long)tile * TT + koff + t, key);
-                  atomicMin(cdist + (long long)tile * TT + koff + t, mn);
-                  atomicMin(filt + koff + t, mn);
-                }
-              }
-            }
-          }
+          if (__any_sync(FULL, ev))
+            sym_column_update(u0, u1, u2, u3, h0, h1, h2, h3, lane, group, ckeys, cdist, filt, tile * TT, koff);
         }
         const int cbase = tile * TT + ch * C;
 #pragma unroll
         for (int q = 0; q < QPT; ++q) {
-          if (NND_MIN_VARIANT == 5) cm[q] = -cm[q];
           if (cm[q] < best[q]) bchunk[q] = cbase;
           best[q] = fminf(best[q], cm[q]);
         }
