@@ -222,7 +222,7 @@ def run_b200_arm(args, w):
         else:
             # rank 0's clouds are broadcast (NCCL over NVLink), rows sharded, results gathered / all-reduced
             d1, d2, i1, i2, info = sharded.sharded_forward(x1, x2, src=0, gather=True)
-            launches[0] += 2 * 3
+            launches[0] += 4  # prepare, symmetric scan, row finalize, column finalize
             g1, g2 = sharded.sharded_backward(x1, x2, gd1, gd2, i1, i2, info, gathered=True)
             launches[0] += 2
         return d1, d2, g1, g2
@@ -343,8 +343,10 @@ def run_b200_arm(args, w):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": w["desc"], "cloud": w["kind"], "b": b, "n": n, "m": m,
                        "pairs_per_step": pairs, "l2": "256 MB buffer rewritten between timed steps (L2 flush)",
-                       "parallelism": "query rows sharded over ranks; NCCL broadcast of both clouds, all_gather of "
-                                      "dist/idx, all_reduce of gradients" if world > 1 else "single GPU"},
+                       "parallelism": "xyz1 rows sharded over ranks (symmetric scan: each rank evaluates its rows x all "
+                                      "columns once); NCCL broadcast of both clouds, int64 MIN all_reduce of the "
+                                      "column keys, all_gather of dist1/idx1, SUM all_reduce of gradients"
+                                      if world > 1 else "single GPU"},
             "roofline": {"bound": "fp32", "kernel": "nnd_scan_sym_kernel", "achieved": achieved, "peak": peak,
                          "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                          "peak_source": f"148 SM x 128 FP32 lanes x sm_max_mhz {sm_max_mhz:.0f} MHz, {peak_src}; FMA is "
