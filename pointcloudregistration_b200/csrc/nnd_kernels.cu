@@ -417,72 +417,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
 // ----------------------------------------------------------------------------------
 // backward
 // ----------------------------------------------------------------------------------
-struct GradTerm {
-  const float* q;      // [b][nq][3]  rows of this term
-  const float* t;      // [b][nt][3]  the other cloud
-  const float* gd;     // [b][nq]
-  const int32_t* idx;  // [b][nq]
-  float* gq;           // [b][nq][3]
-  float* gt;           // [b][nt][3]
-  int nq, nt;
-  long long rows;  // b * nq
-};
-struct GradParams {
-  GradTerm t[2];
-  int nterms;
-};
-
-// my_lib.cpp:96-129 / nnd_cuda.cu:164-183: t = (2*graddist) * (q - target[idx]) per component,
-// grad_q[row] += t, grad_t[idx] -= t.  Scatter side: lanes of a warp that hit the same
-// target row are combined first (match.any), one lane issues the atomics.
-__global__ void __launch_bounds__(256) nnd_grad_kernel(GradParams p) {
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  const unsigned lane = threadIdx.x & 31u;
-  for (int ti = 0; ti < p.nterms; ++ti) {
-    const GradTerm t = p.t[ti];
-    const long long rows_pad = (t.rows + 31) & ~31ll;  // whole warps stay converged for match/shfl
-    for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < rows_pad; r += stride) {
-      const bool live = r < t.rows;
-      float tx = 0.f, ty = 0.f, tz = 0.f;
-      long long trow = -1 - (long long)lane;  // dead lanes never match anybody
-      if (live) {
-        const long long batch = r / t.nq;
-        const int j2 = t.idx[r];
-        trow = batch * t.nt + j2;
-        const float* a = t.q + r * 3;
-        const float* b = t.t + trow * 3;
-        const float g = __fmul_rn(t.gd[r], 2.0f);
-        tx = __fmul_rn(g, __fsub_rn(a[0], b[0]));
-        ty = __fmul_rn(g, __fsub_rn(a[1], b[1]));
-        tz = __fmul_rn(g, __fsub_rn(a[2], b[2]));
-        float* go = t.gq + r * 3;
-        atomicAdd(go + 0, tx);
-        atomicAdd(go + 1, ty);
-        atomicAdd(go + 2, tz);
-      }
-      const unsigned peers = __match_any_sync(0xffffffffu, trow);
-      const unsigned leader = __ffs(peers) - 1;
-      float sx = tx, sy = ty, sz = tz;
-      if (peers != (1u << lane)) {  // somebody shares my target row: leader sums the group
-        sx = sy = sz = 0.f;
-        unsigned rest = peers;
-        while (rest) {  // same trip count for all lanes of a group; other groups diverge harmlessly
-          const int src = __ffs(rest) - 1;
-          rest &= rest - 1;
-          sx += __shfl_sync(peers, tx, src);
-          sy += __shfl_sync(peers, ty, src);
-          sz += __shfl_sync(peers, tz, src);
-        }
-      }
-      if (live && lane == leader) {
-        float* gt = t.gt + trow * 3;
-        atomicAdd(gt + 0, -sx);
-        atomicAdd(gt + 1, -sy);
-        atomicAdd(gt + 2, -sz);
-      }
-    }
-  }
-}
+#include "nnd_grad.cuh"
 
 // ----------------------------------------------------------------------------------
 // host side
@@ -747,16 +682,33 @@ int zero_outputs(float* dist, int32_t* idx, long long count, cudaStream_t st) {
   return check_last(e);
 }
 
-int launch_grad(const GradParams& gp, cudaStream_t st) {
+inline unsigned grad_grid(const GradParams& gp, int sms) {
+  long long rows = 0;
+  for (int i = 0; i < gp.nterms; ++i) rows = gp.t[i].rows > rows ? gp.t[i].rows : rows;
+  long long blocks = (rows + kGradThreads - 1) / kGradThreads;
+  if (blocks > (long long)sms * 8) blocks = (long long)sms * 8;
+  return (unsigned)(blocks < 1 ? 1 : blocks);
+}
+
+// Full backward: own-row stores (overwrite both outputs) then neighbour-side reductions.
+int launch_grad_full(const GradParams& gp, cudaStream_t st) {
   DeviceInfo di;
   int rc = device_info(&di);
   if (rc) return rc;
-  long long rows = 0;
-  for (int i = 0; i < gp.nterms; ++i) rows = gp.t[i].rows > rows ? gp.t[i].rows : rows;
-  if (rows == 0) return 0;
-  long long blocks = (rows + 255) / 256;
-  if (blocks > (long long)di.sms * 8) blocks = (long long)di.sms * 8;
-  nnd_grad_kernel<<<(unsigned)blocks, 256, 0, st>>>(gp);
+  const unsigned grid = grad_grid(gp, di.sms);
+  nnd_grad_own_kernel<<<grid, kGradThreads, 0, st>>>(gp);
+  ++g_launches;
+  nnd_grad_scatter_kernel<false><<<grid, kGradThreads, 0, st>>>(gp);
+  ++g_launches;
+  return check_last(cudaGetLastError());
+}
+
+// One term, accumulating into caller-zeroed buffers (both sides as reductions).
+int launch_grad_term(const GradParams& gp, cudaStream_t st) {
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  nnd_grad_scatter_kernel<true><<<grad_grid(gp, di.sms), kGradThreads, 0, st>>>(gp);
   ++g_launches;
   return check_last(cudaGetLastError());
 }
@@ -899,7 +851,7 @@ int nnd_backward_term_cuda_f32(const float* query, const float* target, const fl
   GradParams gp{};
   gp.nterms = 1;
   gp.t[0] = GradTerm{query, target, graddist, idx, grad_query, grad_target, nq, nt, (long long)b * nq};
-  return launch_grad(gp, (cudaStream_t)stream);
+  return launch_grad_term(gp, (cudaStream_t)stream);
 }
 
 int nnd_backward_cuda_f32(const float* xyz1, const float* xyz2, const float* graddist1, const float* graddist2,
@@ -909,24 +861,19 @@ int nnd_backward_cuda_f32(const float* xyz1, const float* xyz2, const float* gra
   if (b < 0 || n < 0 || m < 0) return NND_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   if (b == 0) return 0;
-  cudaError_t e;
-  if (n > 0) {
-    if (!gradxyz1) return NND_EINVAL;
-    e = cudaMemsetAsync(gradxyz1, 0, (size_t)b * n * 3 * sizeof(float), st);
-    if (e != cudaSuccess) return (int)e;
+  if ((n > 0 && !gradxyz1) || (m > 0 && !gradxyz2)) return NND_EINVAL;
+  if (n == 0 || m == 0) {  // no pairs: both gradients are zero (my_lib.cpp:91-94 with empty loops)
+    cudaError_t e = cudaSuccess;
+    if (n > 0) e = cudaMemsetAsync(gradxyz1, 0, (size_t)b * n * 3 * sizeof(float), st);
+    if (m > 0 && e == cudaSuccess) e = cudaMemsetAsync(gradxyz2, 0, (size_t)b * m * 3 * sizeof(float), st);
+    return check_last(e);
   }
-  if (m > 0) {
-    if (!gradxyz2) return NND_EINVAL;
-    e = cudaMemsetAsync(gradxyz2, 0, (size_t)b * m * 3 * sizeof(float), st);
-    if (e != cudaSuccess) return (int)e;
-  }
-  if (n == 0 || m == 0) return 0;  // no pairs: both gradients are zero
   if (!xyz1 || !xyz2 || !graddist1 || !graddist2 || !idx1 || !idx2) return NND_EINVAL;
   GradParams gp{};
   gp.nterms = 2;
   gp.t[0] = GradTerm{xyz1, xyz2, graddist1, idx1, gradxyz1, gradxyz2, n, m, (long long)b * n};
   gp.t[1] = GradTerm{xyz2, xyz1, graddist2, idx2, gradxyz2, gradxyz1, m, n, (long long)b * m};
-  return launch_grad(gp, st);
+  return launch_grad_full(gp, st);  // the own-row kernel overwrites both outputs: no memset
 }
 
 }  // extern "C"
