@@ -682,33 +682,17 @@ int zero_outputs(float* dist, int32_t* idx, long long count, cudaStream_t st) {
   return check_last(e);
 }
 
-inline unsigned grad_grid(const GradParams& gp, int sms) {
+int launch_grad(const GradParams& gp, cudaStream_t st) {
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
   long long rows = 0;
   for (int i = 0; i < gp.nterms; ++i) rows = gp.t[i].rows > rows ? gp.t[i].rows : rows;
-  long long blocks = (rows + kGradThreads - 1) / kGradThreads;
-  if (blocks > (long long)sms * 8) blocks = (long long)sms * 8;
-  return (unsigned)(blocks < 1 ? 1 : blocks);
-}
-
-// Full backward: own-row stores (overwrite both outputs) then neighbour-side reductions.
-int launch_grad_full(const GradParams& gp, cudaStream_t st) {
-  DeviceInfo di;
-  int rc = device_info(&di);
-  if (rc) return rc;
-  const unsigned grid = grad_grid(gp, di.sms);
-  nnd_grad_own_kernel<<<grid, kGradThreads, 0, st>>>(gp);
-  ++g_launches;
-  nnd_grad_scatter_kernel<false><<<grid, kGradThreads, 0, st>>>(gp);
-  ++g_launches;
-  return check_last(cudaGetLastError());
-}
-
-// One term, accumulating into caller-zeroed buffers (both sides as reductions).
-int launch_grad_term(const GradParams& gp, cudaStream_t st) {
-  DeviceInfo di;
-  int rc = device_info(&di);
-  if (rc) return rc;
-  nnd_grad_scatter_kernel<true><<<grad_grid(gp, di.sms), kGradThreads, 0, st>>>(gp);
+  if (rows == 0) return 0;
+  const long long span = (long long)kGradThreads * kGradRows;
+  long long blocks = (rows + span - 1) / span;
+  if (blocks > (long long)di.sms * 8) blocks = (long long)di.sms * 8;
+  nnd_grad_kernel<<<(unsigned)blocks, kGradThreads, 0, st>>>(gp);
   ++g_launches;
   return check_last(cudaGetLastError());
 }
@@ -851,7 +835,7 @@ int nnd_backward_term_cuda_f32(const float* query, const float* target, const fl
   GradParams gp{};
   gp.nterms = 1;
   gp.t[0] = GradTerm{query, target, graddist, idx, grad_query, grad_target, nq, nt, (long long)b * nq};
-  return launch_grad_term(gp, (cudaStream_t)stream);
+  return launch_grad(gp, (cudaStream_t)stream);
 }
 
 int nnd_backward_cuda_f32(const float* xyz1, const float* xyz2, const float* graddist1, const float* graddist2,
@@ -862,18 +846,17 @@ int nnd_backward_cuda_f32(const float* xyz1, const float* xyz2, const float* gra
   cudaStream_t st = (cudaStream_t)stream;
   if (b == 0) return 0;
   if ((n > 0 && !gradxyz1) || (m > 0 && !gradxyz2)) return NND_EINVAL;
-  if (n == 0 || m == 0) {  // no pairs: both gradients are zero (my_lib.cpp:91-94 with empty loops)
-    cudaError_t e = cudaSuccess;
-    if (n > 0) e = cudaMemsetAsync(gradxyz1, 0, (size_t)b * n * 3 * sizeof(float), st);
-    if (m > 0 && e == cudaSuccess) e = cudaMemsetAsync(gradxyz2, 0, (size_t)b * m * 3 * sizeof(float), st);
-    return check_last(e);
-  }
+  cudaError_t e = cudaSuccess;  // zero-init fused into the call (my_lib.cpp:91-94)
+  if (n > 0) e = cudaMemsetAsync(gradxyz1, 0, (size_t)b * n * 3 * sizeof(float), st);
+  if (m > 0 && e == cudaSuccess) e = cudaMemsetAsync(gradxyz2, 0, (size_t)b * m * 3 * sizeof(float), st);
+  if (e != cudaSuccess) return (int)e;
+  if (n == 0 || m == 0) return 0;  // no pairs: both gradients are zero
   if (!xyz1 || !xyz2 || !graddist1 || !graddist2 || !idx1 || !idx2) return NND_EINVAL;
   GradParams gp{};
   gp.nterms = 2;
   gp.t[0] = GradTerm{xyz1, xyz2, graddist1, idx1, gradxyz1, gradxyz2, n, m, (long long)b * n};
   gp.t[1] = GradTerm{xyz2, xyz1, graddist2, idx2, gradxyz2, gradxyz1, m, n, (long long)b * m};
-  return launch_grad_full(gp, st);  // the own-row kernel overwrites both outputs: no memset
+  return launch_grad(gp, st);
 }
 
 }  // extern "C"
