@@ -444,6 +444,25 @@ constexpr int kChunk = NND_CHUNK;
 constexpr int kStages = NND_STAGES;
 constexpr int kMinBlocks = NND_MINB;
 constexpr int kQB = kThreads * kQPT;
+constexpr int kRowAlign = 8;  // row ranges of the multi-GPU path start on multiples of this (a multiple of every QPT)
+
+// Work shapes.  The large shape is the throughput kernel; the two small ones exist because a (query block x target
+// tile) unit of 2048 x 512 leaves most of the 148 SMs idle on the clouds the reference's callers really use
+// (DIP patches B=256,N=M=256; NDP clouds ~3 k points): fewer rows per thread -> more, smaller units.
+enum ScanShape { kShapeLarge = 0, kShapeMid = 1, kShapeSmall = 2 };
+struct ShapeInfo {
+  int threads, qpt, minb;
+};
+constexpr ShapeInfo kShapes[3] = {{kThreads, kQPT, kMinBlocks}, {256, 2, 4}, {128, 2, 8}};
+
+// Chosen from the GLOBAL problem size only (never from a rank's row range): every rank of the multi-GPU path must
+// use the same row-group size, because column keys carry row-group ids.
+inline ScanShape choose_shape(int b, int n, int m, int sms) {
+  const long long units_large = (long long)b * ((n + kQB - 1) / kQB) * ((m + kTT - 1) / kTT);
+  if (units_large >= 4ll * sms) return kShapeLarge;
+  if (n <= 256) return kShapeSmall;
+  return kShapeMid;
+}
 
 thread_local int g_launches = 0;
 
@@ -510,6 +529,33 @@ inline unsigned grid_for(long long items, int sms) {
   return (unsigned)(blocks < 1 ? 1 : blocks);
 }
 
+template <int THREADS, int QPT, int MINB>
+int launch_sym(const SymParams& yp, int grid, size_t smem, cudaStream_t st) {
+  auto kern = nnd_scan_sym_kernel<THREADS, QPT, kTT, kChunk, kStages, MINB>;
+  static bool attr_set[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    attr_set[dev & 63] = true;
+  }
+  kern<<<grid, THREADS, smem, st>>>(yp);
+  return 0;
+}
+
+template <int THREADS, int QPT, int MINB>
+void launch_scan(const ScanParams& sp, int grid, cudaStream_t st) {
+  nnd_scan_kernel<THREADS, QPT, kTT, kChunk, kStages, MINB><<<grid, THREADS, 0, st>>>(sp);
+}
+
+inline bool use_symmetric(int n, int m);
+// Shape of the symmetric kernel: the large one whenever the single-GPU entry point would pick the symmetric path
+// (more rows per warp step = fewer column slow paths); small clouds only get here through the row-range entry point.
+inline ScanShape sym_shape(int b, int n, int m, int sms) {
+  return use_symmetric(n, m) ? kShapeLarge : choose_shape(b, n, m, sms);
+}
+
 // Symmetric forward over the row range [row_lo, row_hi) of xyz1 (every batch element):
 //   prepare (SoA copies, key/filter init) -> nnd_scan_sym_kernel -> nnd_finalize_kernel for those rows.
 // colkeys receives this launch's column keys; finalize_cols_impl turns (merged) column keys into dist2/idx2.
@@ -572,22 +618,21 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   yp.row_hi = row_hi;
   yp.qtiles = tiles_of(n1);
   yp.ttiles = tiles_of(n2);
-  yp.qblocks = (nrows + kQB - 1) / kQB;
+  const ScanShape shape = sym_shape(b, n1, n2, di.sms);
+  const ShapeInfo si = kShapes[shape];
+  const int qb = si.threads * si.qpt;
+  yp.qblocks = (nrows + qb - 1) / qb;
   yp.total_units = (long long)b * yp.qblocks * yp.ttiles;
   yp.one = 1.0f;
-  const int grid_full = di.sms * kMinBlocks;
+  const int grid_full = di.sms * si.minb;
   const int grid = yp.total_units < grid_full ? (int)yp.total_units : grid_full;
   const size_t smem = sizeof(SymStage<kTT>) * kStages;
-  static bool attr_set[64] = {};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (!attr_set[dev & 63]) {
-    cudaError_t e = cudaFuncSetAttribute(nnd_scan_sym_kernel<kThreads, kQPT, kTT, kChunk, kStages, kMinBlocks>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    attr_set[dev & 63] = true;
+  switch (shape) {
+    case kShapeLarge: rc = launch_sym<kThreads, kQPT, kMinBlocks>(yp, grid, smem, st); break;
+    case kShapeMid: rc = launch_sym<256, 2, 4>(yp, grid, smem, st); break;
+    default: rc = launch_sym<128, 2, 8>(yp, grid, smem, st); break;
   }
-  nnd_scan_sym_kernel<kThreads, kQPT, kTT, kChunk, kStages, kMinBlocks><<<grid, kThreads, smem, st>>>(yp);
+  if (rc) return rc;
   ++g_launches;
   if (ev) cudaEventRecord(ev[2], st);
   debug_sync("scan_sym", st);
@@ -609,22 +654,28 @@ int finalize_cols_impl(const float* c1, int n1, const float* c2, int n2, int b, 
   int rc = device_info(&di);
   if (rc) return rc;
   FinColParams cp{colkeys, c1, c2, dist2, idx2, n1, n2, tiles_of(n2), (long long)b * n2, 1.0f};
-  nnd_finalize_cols_kernel<kTT, kQPT><<<grid_for(cp.count, di.sms), 256, 0, st>>>(cp);
+  if (kShapes[sym_shape(b, n1, n2, di.sms)].qpt == kQPT)
+    nnd_finalize_cols_kernel<kTT, kQPT><<<grid_for(cp.count, di.sms), 256, 0, st>>>(cp);
+  else
+    nnd_finalize_cols_kernel<kTT, 2><<<grid_for(cp.count, di.sms), 256, 0, st>>>(cp);
   ++g_launches;
   debug_sync("finalize_cols", st);
   return check_last(cudaGetLastError());
 }
 
 // One direction (nnd_query_cuda_f32): prepare + nnd_scan_kernel + finalize.
-int query_impl(const float* q, int nq, const float* t, int nt, int b, float* dist, int32_t* idx, void* workspace,
-               size_t workspace_bytes, cudaStream_t st) {
+// Two-pass forward: every direction scans the other cloud separately (nnd_scan_kernel; no column bookkeeping).
+// ndir == 1: for every q point its nearest t point.  ndir == 2: additionally for every t point its nearest q point
+// (dist2/idx2); used for clouds too small for the symmetric kernel to pay off (see use_symmetric()).
+int twopass_impl(const float* q, int nq, const float* t, int nt, int b, int ndir, float* dist, int32_t* idx,
+                 float* dist2, int32_t* idx2, void* workspace, size_t workspace_bytes, cudaStream_t st) {
   cudaEvent_t* ev = nullptr;
   if (g_prof.enabled && g_prof.used < kProfSlots) ev = &g_prof.ev[4 * g_prof.used++];
   DeviceInfo di;
   int rc = device_info(&di);
   if (rc) return rc;
   if (((uintptr_t)workspace & 255u) != 0) return NND_EWORKSPACE;
-  const size_t need = soa_bytes(b, nq) + soa_bytes(b, nt) + key_bytes(b, nq);
+  const size_t need = soa_bytes(b, nq) + soa_bytes(b, nt) + key_bytes(b, nq) + (ndir == 2 ? key_bytes(b, nt) : 0);
   if (workspace_bytes < need) return NND_EWORKSPACE;
   char* w = (char*)workspace;
   float* soaq = (float*)w;
@@ -632,6 +683,8 @@ int query_impl(const float* q, int nq, const float* t, int nt, int b, float* dis
   float* soat = (float*)w;
   w += soa_bytes(b, nt);
   unsigned long long* keys = (unsigned long long*)w;
+  w += key_bytes(b, nq);
+  unsigned long long* keys2 = ndir == 2 ? (unsigned long long*)w : nullptr;
 
   PrepParams pp{};
   pp.nclouds = 2;
@@ -639,6 +692,8 @@ int query_impl(const float* q, int nq, const float* t, int nt, int b, float* dis
   pp.c[1] = PrepCloud{t, soat, nt, tiles_of(nt), (long long)b * tiles_of(nt) * kTT};
   pp.fill64[0] = keys;
   pp.count64[0] = (long long)b * nq;
+  pp.fill64[1] = keys2;
+  pp.count64[1] = ndir == 2 ? (long long)b * nt : 0;
   {
     long long total = pp.c[0].padded_total > pp.c[1].padded_total ? pp.c[0].padded_total : pp.c[1].padded_total;
     if (ev) cudaEventRecord(ev[0], st);
@@ -646,33 +701,57 @@ int query_impl(const float* q, int nq, const float* t, int nt, int b, float* dis
     ++g_launches;
     if (ev) cudaEventRecord(ev[1], st);
   }
+  const ScanShape shape = choose_shape(b, nq, nt, di.sms);
+  const ShapeInfo si = kShapes[shape];
+  const int qb = si.threads * si.qpt;
   ScanParams sp{};
-  sp.ndir = 1;
+  sp.ndir = ndir;
   sp.one = 1.0f;
   sp.d[0].qsoa = soaq;
   sp.d[0].tsoa = soat;
   sp.d[0].keys = keys;
   sp.d[0].nq = nq;
   sp.d[0].nt = nt;
-  sp.d[0].qtiles = tiles_of(nq);
-  sp.d[0].ttiles = tiles_of(nt);
-  sp.d[0].qblocks = (nq + kQB - 1) / kQB;
-  sp.d[0].units = (long long)b * sp.d[0].qblocks * sp.d[0].ttiles;
-  sp.total_units = sp.d[0].units;
-  const int grid_full = di.sms * kMinBlocks;
+  sp.d[1].qsoa = soat;
+  sp.d[1].tsoa = soaq;
+  sp.d[1].keys = keys2;
+  sp.d[1].nq = nt;
+  sp.d[1].nt = nq;
+  sp.total_units = 0;
+  for (int i = 0; i < ndir; ++i) {
+    ScanDir& d = sp.d[i];
+    d.qtiles = tiles_of(d.nq);
+    d.ttiles = tiles_of(d.nt);
+    d.qblocks = (d.nq + qb - 1) / qb;
+    d.units = (long long)b * d.qblocks * d.ttiles;
+    sp.total_units += d.units;
+  }
+  const int grid_full = di.sms * si.minb;
   const int grid = sp.total_units < grid_full ? (int)sp.total_units : grid_full;
-  nnd_scan_kernel<kThreads, kQPT, kTT, kChunk, kStages, kMinBlocks><<<grid, kThreads, 0, st>>>(sp);
+  switch (shape) {
+    case kShapeLarge: launch_scan<kThreads, kQPT, kMinBlocks>(sp, grid, st); break;
+    case kShapeMid: launch_scan<256, 2, 4>(sp, grid, st); break;
+    default: launch_scan<128, 2, 8>(sp, grid, st); break;
+  }
   ++g_launches;
   if (ev) cudaEventRecord(ev[2], st);
   FinParams fp{};
-  fp.ndir = 1;
+  fp.ndir = ndir;
   fp.one = 1.0f;
   fp.d[0] = FinDir{keys, q, soat, dist, idx, nq, tiles_of(nt), 0, nq, (long long)b * nq};
-  nnd_finalize_kernel<kTT, kChunk><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
+  if (ndir == 2) fp.d[1] = FinDir{keys2, t, soaq, dist2, idx2, nt, tiles_of(nq), 0, nt, (long long)b * nt};
+  const long long most = ndir == 2 && fp.d[1].count > fp.d[0].count ? fp.d[1].count : fp.d[0].count;
+  nnd_finalize_kernel<kTT, kChunk><<<grid_for(most, di.sms), 256, 0, st>>>(fp);
   ++g_launches;
   if (ev) cudaEventRecord(ev[3], st);
   return check_last(cudaGetLastError());
 }
+
+// The symmetric kernel evaluates every distance once but pays a warp-collective slow path whenever a column
+// minimum improves: about ln(rows / rows-per-warp-step) times per column.  That is < 1 % of the steps for large clouds
+// and most of them for small ones (measured: 86 us at N=M=2048 against 13 us of arithmetic), so small clouds take the
+// two-pass kernel (twice the arithmetic, no bookkeeping).
+inline bool use_symmetric(int n, int m) { return n >= 8192 && m >= 8192; }
 
 int zero_outputs(float* dist, int32_t* idx, long long count, cudaStream_t st) {
   if (count <= 0) return 0;
@@ -731,7 +810,7 @@ size_t nnd_colkeys_count(int b, int m) {
   return colkey_count(b, m);
 }
 
-int nnd_row_group(void) { return kQPT; }
+int nnd_row_group(void) { return kRowAlign; }
 
 size_t nnd_query_workspace_bytes(int b, int nq, int nt) {
   if (b <= 0 || nq <= 0 || nt <= 0) return 256;
@@ -755,6 +834,8 @@ int nnd_forward_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int
   if (m == 0) return zero_outputs(dist1, idx1, (long long)b * n, st);
   if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2 || !workspace) return NND_EINVAL;
   if (workspace_bytes < nnd_workspace_bytes(b, n, m)) return NND_EWORKSPACE;
+  if (!use_symmetric(n, m))
+    return twopass_impl(xyz1, n, xyz2, m, b, 2, dist1, idx1, dist2, idx2, workspace, workspace_bytes, st);
   const size_t rows_bytes = nnd_rows_workspace_bytes(b, n, m);
   unsigned long long* colkeys = (unsigned long long*)((char*)workspace + rows_bytes);
   int rc = forward_rows_impl(xyz1, n, xyz2, m, b, 0, n, dist1, idx1, colkeys, workspace, rows_bytes, st);
@@ -768,7 +849,7 @@ int nnd_forward_rows_cuda_f32(const float* xyz1, const float* xyz2, int b, int n
   g_launches = 0;
   if (!sizes_ok(b, n, m) || b == 0 || n == 0 || m == 0) return NND_EINVAL;
   if (row_lo < 0 || row_hi < row_lo || row_hi > n) return NND_EINVAL;
-  if (row_lo % kQPT != 0 || (row_hi % kQPT != 0 && row_hi != n)) return NND_EINVAL;  // whole row groups only
+  if (row_lo % kRowAlign != 0 || (row_hi % kRowAlign != 0 && row_hi != n)) return NND_EINVAL;  // whole row groups
   if (!xyz1 || !xyz2 || !dist1 || !idx1 || !colkeys || !workspace) return NND_EINVAL;
   return forward_rows_impl(xyz1, n, xyz2, m, b, row_lo, row_hi, dist1, idx1, colkeys, workspace, workspace_bytes,
                            (cudaStream_t)stream);
@@ -822,7 +903,7 @@ int nnd_query_cuda_f32(const float* query, const float* target, int b, int nq, i
   if (b == 0 || nq == 0) return 0;
   if (nt == 0) return zero_outputs(dist, idx, (long long)b * nq, st);
   if (!query || !target || !dist || !idx || !workspace) return NND_EINVAL;
-  return query_impl(query, nq, target, nt, b, dist, idx, workspace, workspace_bytes, st);
+  return twopass_impl(query, nq, target, nt, b, 1, dist, idx, nullptr, nullptr, workspace, workspace_bytes, st);
 }
 
 int nnd_backward_term_cuda_f32(const float* query, const float* target, const float* graddist, const int32_t* idx,

@@ -70,7 +70,7 @@ def test_forward_kernel_sass_is_bit_exact_form():
         pytest.skip("cuobjdump not available")
     kernels = re.split(r"Function : ", out.stdout)
     scan = [k for k in kernels if "nnd_scan_kernel" in k.split("\n", 1)[0] or "nnd_scan_sym_kernel" in k.split("\n", 1)[0]]
-    assert len(scan) == 2, "nnd_scan_kernel / nnd_scan_sym_kernel not found in the cubin"
+    assert len(scan) >= 2, "nnd_scan_kernel / nnd_scan_sym_kernel not found in the cubin"
     for k in scan:
         ops = re.findall(r"^\s+/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", k, flags=re.M)
         n = {name: sum(1 for o in ops if o.split(".")[0] == name) for name in ("FFMA", "FMUL2", "FADD2", "FFMA2", "FMNMX3")}
