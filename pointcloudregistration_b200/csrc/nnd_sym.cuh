@@ -156,15 +156,19 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
     unsigned long long* ckeys = p.ckeys + (long long)batch * p.ttiles * TT;
     unsigned* cdist = p.cdist + (long long)batch * p.ttiles * TT;
 
+    // A warp whose 32*QPT rows all lie beyond row_hi (ragged last query block of a row range) only keeps the
+    // barriers company: its rows are repeats that can never win.  Warp 0 holds the producer and always has rows.
+    const bool warp_live = p.row_lo + qblock * QB + (tid & ~31) * QPT < p.row_hi;
+
     for (int tile = tile0; tile < tile0 + seg_tiles; ++tile) {
       const int stage = cnt % STAGES;
-      mbar_wait(&full[stage], (cnt / STAGES) & 1);
+      const int nchunks_live = warp_live ? (min(TT, p.m - tile * TT) + C - 1) / C : 0;
+      if (warp_live) mbar_wait(&full[stage], (cnt / STAGES) & 1);
       const float* sx = stages[stage].xyz;
       const float* sy = sx + TT;
       const float* sz = sx + 2 * TT;
       unsigned* filt = stages[stage].filt;
-      const int valid = min(TT, p.m - tile * TT);
-      const int nchunks = (valid + C - 1) / C;
+      const int nchunks = nchunks_live;
 
       for (int ch = 0; ch < nchunks; ++ch) {
         const ulonglong2* cx = reinterpret_cast<const ulonglong2*>(sx + ch * C);
