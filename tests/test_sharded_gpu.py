@@ -62,6 +62,29 @@ def test_row_ranges_merge_to_the_unsharded_result(cuda_lib, device, kind, b, n, 
     assert_forward_exact(tuple(t.cpu().numpy() for t in (d1, d2, i1, i2)), want)
 
 
+@pytest.mark.parametrize("kind", ["uniform", "lattice"])
+def test_row_ranges_at_scale_equal_the_single_launch(cuda_lib, device, kind):
+    """Size-independent property at N=M=262144 (symmetric kernel, large shape): 3 uneven row ranges merged by integer
+    MIN give bit-identical dist/idx to the single-launch forward (which the C5/C4 tests tie to the oracle)."""
+    from pointcloudregistration_b200 import functional as F
+    from pointcloudregistration_b200 import synthetic
+
+    n = m = 262144
+    x1, x2 = synthetic.make_pair(kind, 1, n, m, 73)
+    a, c = x1.to(device), x2.to(device)
+    want = F.nnd_forward_raw(a, c)
+    d1 = torch.empty(1, n, device=device)
+    i1 = torch.empty(1, n, dtype=torch.int32, device=device)
+    merged = None
+    for lo, hi in ((0, 100000), (100000, 100008), (100008, n)):
+        dr, ir, keys = F.nnd_forward_rows_raw(a, c, lo, hi)
+        d1[:, lo:hi], i1[:, lo:hi] = dr, ir
+        merged = keys if merged is None else torch.minimum(merged, keys)
+    d2, i2 = F.nnd_finalize_cols_raw(a, c, merged)
+    for got, w in zip((d1, d2, i1, i2), want):
+        assert torch.equal(got, w)
+
+
 def test_row_range_must_be_whole_groups(cuda_lib, device):
     from pointcloudregistration_b200 import functional as F
 
