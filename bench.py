@@ -118,6 +118,8 @@ def cpu_arm(w, steps: int, warmup: int, seconds_per_step: float, kind: str):
     processes (the reference's pybind entry points hold the GIL) released together by a start time.
     """
     cores = len(os.sched_getaffinity(0))
+    if getattr(cpu_arm, "max_cores", None):
+        cores = min(cores, cpu_arm.max_cores)
     b, n, m = w["b"], w["n"], w["m"]
     per_core_rate = 0.30e9  # pairs/s/core, SURVEY.md §6.2; only used to size the sample
     q = int(seconds_per_step * per_core_rate / (2.0 * b * m))
@@ -167,6 +169,68 @@ def run_reference_arm(args, w):
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------- reference GPU kernel
+def run_reference_cuda_arm(args, w):
+    """Comparison row: the reference's OWN CUDA kernels (nnd_cuda.cu, unmodified, recompiled for
+    sm_100a into oracle/_ref/nnd_ref_cuda.so) driven the way torch_nndistance/__init__.py:11-57 drives them, same
+    metric, same inputs, 1 GPU.  Not a parity oracle (FMA-contracted); the line reports how far its outputs are from
+    the B200 path's (which is bit-exact against the reference CPU code)."""
+    import importlib.util
+
+    import torch
+
+    from pointcloudregistration_b200 import functional as F
+    from pointcloudregistration_b200 import synthetic
+
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    so = ROOT / "oracle" / "_ref" / "nnd_ref_cuda.so"
+    if not so.exists():
+        print(json.dumps({"impl": "reference_cuda", "unavailable": "oracle/_ref/nnd_ref_cuda.so not built"}), flush=True)
+        return
+    spec = importlib.util.spec_from_file_location("nnd_ref_cuda", str(so))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    b, n, m = w["b"], w["n"], w["m"]
+    x1h, x2h = synthetic.make_pair(w["kind"], b, n, m, w["config"])
+    gd1h, gd2h = synthetic.grad_pair(b, n, m, w["config"], mean=True)
+    x1, x2, gd1, gd2 = x1h.to(dev), x2h.to(dev), gd1h.to(dev), gd2h.to(dev)
+
+    def step():
+        d1 = torch.zeros(b, n, device=dev)
+        d2 = torch.zeros(b, m, device=dev)
+        i1 = torch.zeros(b, n, dtype=torch.int32, device=dev)
+        i2 = torch.zeros(b, m, dtype=torch.int32, device=dev)
+        mod.nnd_forward_cuda(x1, x2, d1, d2, i1, i2)  # __init__.py:29
+        g1, g2 = torch.zeros_like(x1), torch.zeros_like(x2)
+        mod.nnd_backward_cuda(x1, x2, g1, g2, gd1, gd2, i1, i2)  # __init__.py:50
+        return d1, d2, i1, i2, g1, g2
+
+    steps, warmup = args.steps, max(args.warmup, 1)
+    for _ in range(warmup):
+        out = step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()  # the reference launches on the legacy default stream, which is torch's default stream
+    for _ in range(steps):
+        out = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    pairs = 2.0 * b * n * m
+    ours = F.nnd_forward_raw(x1, x2)
+    same = {k: float((a == c).float().mean()) for k, a, c in zip(("dist1", "dist2", "idx1", "idx2"), out[:4], ours)}
+    line = {"impl": "reference_cuda", "metric": METRIC, "value": pairs / (ms * 1e-3) / 1e9, "unit": UNIT, "n_gpus": 1,
+            "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": w["desc"], "cloud": w["kind"], "b": b, "n": n, "m": m},
+            "fraction_equal_to_b200_path": same,
+            "note": "reference nnd_cuda.cu unmodified, nvcc defaults (FMA-contracted), sm_100a recompile"}
     print(json.dumps(line), flush=True)
 
 
@@ -329,7 +393,9 @@ def run_b200_arm(args, w):
         # 2 pairs per evaluation it delivers (what the two-pass reference formulation would have had to execute).
         scan_calls_per_step = 1
         scan_ms_avg = scan_ms_total / (steps * scan_calls_per_step)  # average launch duration
-        scan_evals = pairs / 2 / world  # distance evaluations one launch on one GPU executes
+        symmetric = world > 1 or bool(lib.nnd_forward_is_symmetric(n, m))
+        # distance evaluations one launch on one GPU executes (small clouds take the two-pass kernel: every pair)
+        scan_evals = (pairs / 2 if symmetric else pairs) / world
         achieved = scan_evals * FP32_OPS_PER_PAIR / (scan_ms_avg * 1e-3) / 1e12
         peak = fp32_peak / 1e12
         traffic = None
@@ -347,15 +413,17 @@ def run_b200_arm(args, w):
                                       "columns once); NCCL broadcast of both clouds, int64 MIN all_reduce of the "
                                       "column keys, all_gather of dist1/idx1, SUM all_reduce of gradients"
                                       if world > 1 else "single GPU"},
-            "roofline": {"bound": "fp32", "kernel": "nnd_scan_sym_kernel", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "fp32", "kernel": "nnd_scan_sym_kernel" if symmetric else "nnd_scan_kernel",
+                         "achieved": achieved, "peak": peak,
                          "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                          "peak_source": f"148 SM x 128 FP32 lanes x sm_max_mhz {sm_max_mhz:.0f} MHz, {peak_src}; FMA is "
                                         "forbidden by bit-exactness so 1 op = 1 lane-slot (the FMA-flop peak is 2x)",
                          "frac_of_fma_flop_peak": achieved / (2 * peak),
                          "flop_per_launch": scan_evals * FP32_OPS_PER_PAIR, "kernel_ms": scan_ms_avg,
-                         "evaluations_per_launch": scan_evals, "metric_pairs_per_launch": 2 * scan_evals,
-                         "metric_equivalent_achieved": 2 * achieved, "metric_equivalent_frac": 2 * achieved / peak,
-                         "metric_equivalent_frac_of_fma_flop_peak": achieved / peak,
+                         "evaluations_per_launch": scan_evals, "metric_pairs_per_launch": pairs / world,
+                         "metric_equivalent_achieved": achieved * (pairs / world) / scan_evals,
+                         "metric_equivalent_frac": achieved * (pairs / world) / scan_evals / peak,
+                         "metric_equivalent_frac_of_fma_flop_peak": achieved * (pairs / world) / scan_evals / (2 * peak),
                          "kernel_share_of_step": scan_ms_total / world / total_ms if world == 1 else None},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": float(e2e_ms.item()) / steps, "loss": last_loss},
@@ -381,18 +449,22 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
+    ap.add_argument("--impl", choices=["b200", "reference", "reference_cuda"], default="b200")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c4")
     ap.add_argument("--kind", default=None, help="cloud generator override (uniform, clustered, lattice, ...)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU work in the cpu_baseline sample")
+    ap.add_argument("--cpu-cores", type=int, default=0, help="cap the host cores the CPU arm uses (0 = all)")
     ap.add_argument("--cpu-seconds-per-step", type=float, default=3.0, help="--impl reference: CPU work per step")
     args = ap.parse_args()
     w = dict(WORKLOADS[args.workload])
+    cpu_arm.max_cores = args.cpu_cores or None
     if args.kind:
         w["kind"] = args.kind
     if args.impl == "reference":
         run_reference_arm(args, w)
+    elif args.impl == "reference_cuda":
+        run_reference_cuda_arm(args, w)
     else:
         run_b200_arm(args, w)
 

@@ -82,6 +82,11 @@ int nnd_forward_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int
                          float *dist1, float *dist2, int32_t *idx1, int32_t *idx2,
                          void *workspace, size_t workspace_bytes, void *stream);
 
+/* 1 when nnd_forward_cuda_f32 takes the symmetric kernel for clouds of n and m points (every distance evaluated
+ * once: b*n*m evaluations per call), 0 when it takes the two-pass kernel (2*b*n*m evaluations; small clouds).
+ * Results are bit-identical either way; bench.py uses this to count the work a launch executes. */
+int nnd_forward_is_symmetric(int n, int m);
+
 /* Measurement aid for bench.py's roofline block.  While enabled (per calling thread), every forward /
  * query call also records CUDA events on its stream around each of its three kernels (no
  * synchronisation, up to 64 calls are remembered).  nnd_profile_collect waits for those events and

@@ -26,6 +26,7 @@ SIGNATURES = {
     "nnd_rows_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "nnd_colkeys_count": (c_size_t, [c_int, c_int]),
     "nnd_row_group": (c_int, []),
+    "nnd_forward_is_symmetric": (c_int, [c_int, c_int]),
     "nnd_forward_rows_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                            c_void_p, c_void_p, c_size_t, c_void_p]),
     "nnd_finalize_cols_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,

@@ -812,6 +812,8 @@ size_t nnd_colkeys_count(int b, int m) {
 
 int nnd_row_group(void) { return kRowAlign; }
 
+int nnd_forward_is_symmetric(int n, int m) { return use_symmetric(n, m) ? 1 : 0; }
+
 size_t nnd_query_workspace_bytes(int b, int nq, int nt) {
   if (b <= 0 || nq <= 0 || nt <= 0) return 256;
   return soa_bytes(b, nq) + soa_bytes(b, nt) + key_bytes(b, nq);
