@@ -136,7 +136,13 @@ def sharded_forward(xyz1, xyz2, group=None, src=None, gather=True, compute=CudaC
         dist.all_reduce(colkeys, op=dist.ReduceOp.MIN, group=group)
     d2, i2 = compute.finalize_cols(xyz1, xyz2, colkeys)
     if gather:
-        d1, i1 = _gather_rows(d1, n, world, group, align), _gather_rows(i1, n, world, group, align)
+        if world > 1:  # one collective for both row results: dist bits and idx travel as int32 side by side
+            both = _gather_rows(torch.cat([d1.contiguous().view(torch.int32), i1.contiguous()], dim=0), n, world,
+                                group, align)
+            b = xyz1.size(0)
+            d1, i1 = both[:b].clone().view(torch.float32), both[b:].clone()  # own storage each (dtype differs)
+        else:
+            d1, i1 = d1.contiguous(), i1.contiguous()
     else:
         d1, i1 = d1.contiguous(), i1.contiguous()
         d2, i2 = d2[:, lo2:hi2].contiguous(), i2[:, lo2:hi2].contiguous()
@@ -151,8 +157,10 @@ def sharded_backward(xyz1, xyz2, graddist1, graddist2, idx1, idx2, info: ShardIn
     if gathered:
         graddist1, idx1 = graddist1[:, lo1:hi1], idx1[:, lo1:hi1]
         graddist2, idx2 = graddist2[:, lo2:hi2], idx2[:, lo2:hi2]
-    g1 = torch.zeros_like(xyz1)
-    g2 = torch.zeros_like(xyz2)
+    # one flat buffer for both gradients: a single all_reduce instead of two
+    flat = torch.zeros(xyz1.numel() + xyz2.numel(), dtype=xyz1.dtype, device=xyz1.device)
+    g1 = flat[:xyz1.numel()].view_as(xyz1)
+    g2 = flat[xyz1.numel():].view_as(xyz2)
     own1 = torch.zeros(xyz1.size(0), hi1 - lo1, 3, dtype=xyz1.dtype, device=xyz1.device)
     own2 = torch.zeros(xyz2.size(0), hi2 - lo2, 3, dtype=xyz2.dtype, device=xyz2.device)
     compute.backward_term(xyz1[:, lo1:hi1].contiguous(), xyz2, graddist1.contiguous(), idx1.contiguous(), own1, g2)
@@ -160,8 +168,7 @@ def sharded_backward(xyz1, xyz2, graddist1, graddist2, idx1, idx2, info: ShardIn
     g1[:, lo1:hi1] += own1
     g2[:, lo2:hi2] += own2
     if info.world > 1:
-        dist.all_reduce(g1, op=dist.ReduceOp.SUM, group=group)
-        dist.all_reduce(g2, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
     return g1, g2
 
 
