@@ -39,6 +39,23 @@ template<int MODE,int NX> __global__ void __launch_bounds__(256,2) kern(float* o
       if(MODE==8){ float4 v=*reinterpret_cast<const float4*>(&sm[((it+x)&255)*4]); asm volatile("":"+f"(e[x&7]):"f"(v.x),"f"(v.y),"f"(v.z),"f"(v.w)); e[x&7]=v.x; } // LDS.128 (broadcast)
       if(MODE==9) asm volatile("{.reg .s32 t; min.s32 t,%1,%2; min.s32 %0,%0,t;}":"+r"(ei[x&7]):"r"(__float_as_int(lo)),"r"(__float_as_int(hi))); // 2x IMNMX (maybe VIMNMX3)
       if(MODE==10) asm volatile("max.f32 %0,%0,%1;":"+f"(e[x&7]):"f"(lo));  // FMNMX max
+      if(MODE==11) asm volatile("min.xorsign.abs.f32 %0,%0,%1;":"+f"(e[x&7]):"f"(lo));  // FMNMX.XORSIGN
+      if(MODE==12) asm volatile("min.NaN.f32 %0,%0,%1;":"+f"(e[x&7]):"f"(lo));          // FMNMX.NAN
+      if(MODE==13) asm volatile("{.reg .f32 t; neg.f32 t,%1; max.f32 %0,%0,t;}":"+f"(e[x&7]):"f"(lo)); // FMNMX with -src
+      if(MODE==14){ // chain on ONE accumulator alternating flavours (cannot merge into FMNMX3): 2 inputs per extra op
+        asm volatile("min.f32 %0,%0,%1;":"+f"(e[x&7]):"f"(lo));
+        asm volatile("min.NaN.f32 %0,%0,%1;":"+f"(e[x&7]):"f"(hi)); }
+      if(MODE==16) asm volatile("min.f32 %0,%0,%1;":"+f"(e[x&7]):"f"(hi));   // FMNMX on the ODD half only
+      if(MODE==17){ float lo2,hi2; upk(w[(x+1)&7],lo2,hi2);                     // FMNMX3 on two EVEN halves
+        asm volatile("min.f32 %0,%0,%1,%2;":"+f"(e[x&7]):"f"(lo),"f"(lo2)); }
+      if(MODE==18){ float lo2,hi2; upk(w[(x+1)&7],lo2,hi2);                     // dependent pair, even halves only
+        float t; asm volatile("min.f32 %0,%1,%2;":"=f"(t):"f"(lo),"f"(lo2));
+        asm volatile("min.NaN.f32 %0,%0,%1;":"+f"(e[x&7]):"f"(t)); }
+      if(MODE==19){ float lo2,hi2; upk(w[(x+1)&7],lo2,hi2);                     // FMNMX3 on two ODD halves
+        asm volatile("min.f32 %0,%0,%1,%2;":"+f"(e[x&7]):"f"(hi),"f"(hi2)); }
+      if(MODE==15){ // tree: t=min(lo,hi) plain, e=min.NaN(e,t)
+        float t; asm volatile("min.f32 %0,%1,%2;":"=f"(t):"f"(lo),"f"(hi));
+        asm volatile("min.NaN.f32 %0,%0,%1;":"+f"(e[x&7]):"f"(t)); }
     }
   }
   float s=0; int si=0;
@@ -69,6 +86,7 @@ int main(){
   cudaDeviceProp p; CK(cudaGetDeviceProperties(&p,0)); int nsm=p.multiProcessorCount;
   // warm the clocks for ~1 s
   for(int i=0;i<30;i++) run<0,0>("warm",nsm);
+  printf("(warm-up lines above)\n");
   printf("---- measurements (256 thr x 2 CTA/SM, 8 chains/thread)\n");
   run<0,0>("packed only",nsm);
   run<1,1>("FMNMX3",nsm); run<1,2>("FMNMX3",nsm); run<1,4>("FMNMX3",nsm);
@@ -81,6 +99,17 @@ int main(){
   run<6,2>("IADD",nsm); run<6,4>("IADD",nsm);
   run<7,2>("FADD scalar",nsm); run<7,4>("FADD scalar",nsm);
   run<8,1>("LDS.128",nsm); run<8,2>("LDS.128",nsm);
+  run<11,2>("FMNMX.XORSIGN",nsm); run<11,4>("FMNMX.XORSIGN",nsm);
+  run<12,2>("FMNMX.NAN",nsm); run<12,4>("FMNMX.NAN",nsm); run<12,8>("FMNMX.NAN",nsm);
+  run<2,8>("FMNMX",nsm);
+  run<13,2>("FMNMX(-src)",nsm); run<13,4>("FMNMX(-src)",nsm);
+  run<14,2>("min+min.NaN chain (2 ops)",nsm); run<14,4>("min+min.NaN chain (2 ops)",nsm);
+  run<15,2>("min tree + min.NaN (2 ops)",nsm); run<15,4>("min tree + min.NaN (2 ops)",nsm);
+  run<16,2>("FMNMX odd half",nsm); run<16,4>("FMNMX odd half",nsm);
+  run<17,2>("FMNMX3 even+even",nsm); run<17,4>("FMNMX3 even+even",nsm);
+  run<19,2>("FMNMX3 odd+odd",nsm);
+  run<18,2>("dep. pair even only",nsm); run<18,4>("dep. pair even only",nsm);
+  run<1,2>("FMNMX3 (again)",nsm);
   run<0,0>("packed only (again)",nsm);
   return 0;
 }
