@@ -41,9 +41,6 @@
 
 #include "nnd_b200.h"
 
-#ifndef NND_MIN_VARIANT
-#define NND_MIN_VARIANT 0
-#endif
 #define NND_VERSION_STRING "nnd_b200 0.1.0 sm_100a"
 
 namespace {
