@@ -429,7 +429,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
 #define NND_MINB 2
 #endif
 #ifndef NND_STAGES
-#define NND_STAGES 4
+#define NND_STAGES 2
 #endif
 constexpr int kThreads = NND_THREADS;
 constexpr int kQPT = NND_QPT;
