@@ -433,7 +433,10 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
 #endif
 constexpr int kThreads = NND_THREADS;
 constexpr int kQPT = NND_QPT;
-constexpr int kTT = 512;
+#ifndef NND_TT
+#define NND_TT 512
+#endif
+constexpr int kTT = NND_TT;
 #ifndef NND_CHUNK
 #define NND_CHUNK 32
 #endif
