@@ -73,9 +73,14 @@ __device__ __noinline__ void sym_column_update(unsigned u0, unsigned u1, unsigne
       const unsigned holders = __ballot_sync(FULL, uu[t] == mn);
       if (lane == (unsigned)(__ffs(holders) - 1)) {  // lowest lane = lowest row group
         const unsigned long long key = ((unsigned long long)mn << 32) | group;
-        atomicMin(ckeys + (long long)tile_base + koff + t, key);
-        atomicMin(cdist + (long long)tile_base + koff + t, mn);
-        atomicMin(filt + koff + t, mn);
+        unsigned long long* kp = ckeys + (long long)tile_base + koff + t;
+        // An exact tie with the filter can only matter if this group is lower than the recorded one: look before
+        // posting, so that degenerate clouds (many identical points) do not turn every step into three atomics.
+        if (mn < hh[t] || key < *reinterpret_cast<volatile unsigned long long*>(kp)) {
+          atomicMin(kp, key);
+          atomicMin(cdist + (long long)tile_base + koff + t, mn);
+          atomicMin(filt + koff + t, mn);
+        }
       }
     }
   }
