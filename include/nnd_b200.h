@@ -113,6 +113,18 @@ int nnd_backward_cuda_f32(const float *xyz1, const float *xyz2,
                           int b, int n, int m,
                           float *gradxyz1, float *gradxyz2, void *stream);
 
+/* Fused truncated-chamfer epilogue (c2p-net/deformationpyramid/model/loss.py:150-215 with mean/mean reductions, the
+ * form registration.py:236 uses):  loss[0] = scale1 * sum(dist1 < trunc ? dist1 : 0) + scale2 * sum(dist2 < trunc ? dist2 : 0),
+ * and, when the pointers are non-null, graddist1[i] = dist1[i] < trunc ? scale1 : 0 (likewise graddist2): d loss / d dist,
+ * ready for nnd_backward_cuda_f32.  Deterministic (fixed summation order).  `workspace` is
+ * nnd_chamfer_reduce_workspace_bytes() of 256-byte aligned device memory that the caller ZEROES ONCE; the kernel
+ * leaves it ready for the next call. */
+size_t nnd_chamfer_reduce_workspace_bytes(void);
+int nnd_chamfer_reduce_cuda_f32(const float *dist1, const float *dist2, int b, int n, int m,
+                                float trunc, float scale1, float scale2,
+                                float *loss, float *graddist1, float *graddist2,
+                                void *workspace, size_t workspace_bytes, void *stream);
+
 /* One term of the backward (the unit the query-sharded multi-GPU path calls):
  * for query rows [0,nq) with nearest targets idx:  t = 2*graddist*(q - target[idx]);
  * grad_query[row] += t ; grad_target[idx] -= t.  ACCUMULATES (caller zeroes). */

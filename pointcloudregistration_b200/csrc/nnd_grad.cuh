@@ -140,3 +140,58 @@ __global__ void __launch_bounds__(kGradThreads) nnd_grad_kernel(GradParams p) {
     }
   }
 }
+
+// ----------------------------------------------------------------------------------------------------------------
+// Fused truncated-chamfer epilogue (c2p-net/deformationpyramid/model/loss.py:150-215 with point_reduction = batch_reduction
+// = "mean" and no weights, the form registration.py:236 uses):
+//     loss = scale1 * sum_{dist1 < trunc} dist1 + scale2 * sum_{dist2 < trunc} dist2
+//     graddist1 = dist1 < trunc ? scale1 : 0        (d loss / d dist1; the mask is reused by the backward)
+// One launch instead of ~10 elementwise/reduction launches.  Deterministic: per-block partial sums are combined in
+// block order by the last block to finish.
+struct ReduceParams {
+  const float* dist[2];
+  float* graddist[2];  // may be null
+  long long count[2];
+  float scale[2];
+  float trunc;
+  float* loss;       // [1]
+  double* partial;   // [gridDim.x]
+  unsigned* ticket;  // [1], zero before the launch; reset by the kernel
+};
+
+__global__ void __launch_bounds__(256) nnd_chamfer_reduce_kernel(ReduceParams p) {
+  __shared__ double warp_sum[8];
+  __shared__ bool last;
+  double acc = 0.0;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    double a = 0.0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < p.count[k]; i += stride) {
+      const float d = p.dist[k][i];
+      const bool keep = !(d >= p.trunc);  // loss.py:151-154: cham[cham >= trunc] = 0
+      if (keep) a += (double)d;
+      if (p.graddist[k] != nullptr) p.graddist[k][i] = keep ? p.scale[k] : 0.0f;
+    }
+    acc += a * (double)p.scale[k];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int w = 0; w < 8; ++w) s += warp_sum[w];
+    p.partial[blockIdx.x] = s;
+    __threadfence();
+    last = atomicAdd(p.ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (last && threadIdx.x == 0) {
+    __threadfence();
+    double s = 0.0;
+    for (unsigned b = 0; b < gridDim.x; ++b) s += reinterpret_cast<volatile double*>(p.partial)[b];
+    *p.loss = (float)s;
+    *p.ticket = 0u;  // ready for the next launch (and for CUDA-graph replays)
+  }
+}

@@ -508,6 +508,8 @@ inline size_t filter_bytes(int b, int m) { return align_up(colkey_count(b, m) * 
 
 int check_last(cudaError_t e) { return e == cudaSuccess ? 0 : (int)e; }
 
+constexpr int kReduceMaxBlocks = 1024;  // partial sums of nnd_chamfer_reduce_kernel
+
 // NND_B200_DEBUG_SYNC=1: synchronise after every kernel of the forward and report it on stderr (triage aid).
 void debug_sync(const char* what, cudaStream_t st) {
   static int on = -1;
@@ -919,6 +921,41 @@ int nnd_backward_term_cuda_f32(const float* query, const float* target, const fl
   gp.nterms = 1;
   gp.t[0] = GradTerm{query, target, graddist, idx, grad_query, grad_target, nq, nt, (long long)b * nq};
   return launch_grad(gp, (cudaStream_t)stream);
+}
+
+size_t nnd_chamfer_reduce_workspace_bytes(void) { return (size_t)kReduceMaxBlocks * sizeof(double) + 256; }
+
+int nnd_chamfer_reduce_cuda_f32(const float* dist1, const float* dist2, int b, int n, int m, float trunc, float scale1,
+                                float scale2, float* loss, float* graddist1, float* graddist2, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+  g_launches = 0;
+  if (b < 0 || n < 0 || m < 0 || !loss || !workspace) return NND_EINVAL;
+  if (((uintptr_t)workspace & 255u) != 0 || workspace_bytes < nnd_chamfer_reduce_workspace_bytes()) return NND_EWORKSPACE;
+  if (((long long)b * n > 0 && !dist1) || ((long long)b * m > 0 && !dist2)) return NND_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  ReduceParams rp{};
+  rp.dist[0] = dist1;
+  rp.dist[1] = dist2;
+  rp.graddist[0] = graddist1;
+  rp.graddist[1] = graddist2;
+  rp.count[0] = (long long)b * n;
+  rp.count[1] = (long long)b * m;
+  rp.scale[0] = scale1;
+  rp.scale[1] = scale2;
+  rp.trunc = trunc;
+  rp.loss = loss;
+  rp.ticket = (unsigned*)workspace;  // first 256 bytes: the ticket (the caller zeroes the workspace once)
+  rp.partial = (double*)((char*)workspace + 256);
+  const long long most = rp.count[0] > rp.count[1] ? rp.count[0] : rp.count[1];
+  long long blocks = (most + 255) / 256;
+  if (blocks > kReduceMaxBlocks) blocks = kReduceMaxBlocks;
+  if (blocks < 1) blocks = 1;
+  nnd_chamfer_reduce_kernel<<<(unsigned)blocks, 256, 0, st>>>(rp);
+  ++g_launches;
+  return check_last(cudaGetLastError());
 }
 
 int nnd_backward_cuda_f32(const float* xyz1, const float* xyz2, const float* graddist1, const float* graddist2,

@@ -164,6 +164,32 @@ def nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2):
     return gradxyz1, gradxyz2
 
 
+def chamfer_reduce_workspace(device) -> torch.Tensor:
+    """Zeroed scratch for chamfer_reduce_raw; allocate once and reuse (the kernel leaves it zeroed)."""
+    lib = _cabi.load()
+    return torch.zeros(lib.nnd_chamfer_reduce_workspace_bytes(), dtype=torch.uint8, device=device)
+
+
+def chamfer_reduce_raw(dist1, dist2, trunc: float, scale1: float, scale2: float, loss, graddist1, graddist2, ws):
+    """loss[0] = scale1 * sum(dist1 where not >= trunc) + scale2 * (same for dist2); graddist = mask * scale.
+    One launch (c2p-net/deformationpyramid/model/loss.py:150-215 with mean/mean reductions).  All outputs preallocated;
+    graddist1/graddist2 may be None."""
+    lib = _cabi.load()
+    b, n = dist1.shape
+    m = dist2.size(1)
+    dev = dist1.device
+    for t in (dist1, dist2, loss, graddist1, graddist2):
+        if t is not None and (t.dtype != torch.float32 or not t.is_contiguous() or t.device != dev):
+            raise ValueError("chamfer_reduce_raw wants contiguous float32 tensors on one device")
+    with torch.cuda.device(dev):
+        rc = lib.nnd_chamfer_reduce_cuda_f32(dist1.data_ptr(), dist2.data_ptr(), b, n, m, float(trunc), float(scale1),
+                                             float(scale2), loss.data_ptr(),
+                                             graddist1.data_ptr() if graddist1 is not None else None,
+                                             graddist2.data_ptr() if graddist2 is not None else None, ws.data_ptr(),
+                                             ws.numel(), _stream_ptr(dev))
+    _cabi.check(rc, "nnd_chamfer_reduce_cuda_f32")
+
+
 class NNDFunction(Function):
     """torch_nndistance.NNDFunction (reference __init__.py:10-57)."""
 

@@ -11,45 +11,60 @@ over static buffers and replays it: one graph launch per iteration, no allocatio
 stays on the device; read it every k-th iteration (`loss_value()`), which is what makes the early-stop test cheap.
 `ChamferLoopFunction` plugs the replay into autograd so the warp network in front of it trains as before.
 
-Numerics are those of pytorch3d_compat.compute_truncated_chamfer_distance (same kernels, same reduction order).
+Forward and backward are the kernels behind pytorch3d_compat.compute_truncated_chamfer_distance; the mask, the
+mean/mean reduction and d loss / d dist are one fused launch (nnd_chamfer_reduce_cuda_f32: float64 partial sums in a
+fixed order, so the loss is deterministic and agrees with the eager torch reduction to fp32 rounding).
 """
 from __future__ import annotations
 
 import torch
 from torch.autograd import Function
 
-from .functional import nnd_backward_raw, nnd_forward_raw
+from . import _cabi
+from .functional import _stream_ptr, chamfer_reduce_workspace
 
 
 class ChamferLoop:
     def __init__(self, b: int, n: int, m: int, device, trunc: float = 1e9, use_graph: bool = True):
         self.b, self.n, self.m, self.trunc = b, n, m, float(trunc)
-        self.device = torch.device(device)
-        self.x = torch.zeros(b, n, 3, device=self.device)
-        self.y = torch.zeros(b, m, 3, device=self.device)
-        self.loss = torch.zeros((), device=self.device)
+        self.device = dev = torch.device(device)
+        if dev.type != "cuda":
+            raise RuntimeError("ChamferLoop needs a CUDA device: pointcloudregistration_b200 has no CPU path")
+        self.lib = _cabi.load()
+        f32, i32 = dict(dtype=torch.float32, device=dev), dict(dtype=torch.int32, device=dev)
+        self.x = torch.zeros(b, n, 3, **f32)
+        self.y = torch.zeros(b, m, 3, **f32)
+        self.loss = torch.zeros((), **f32)
         self.grad_x = torch.zeros_like(self.x)
         self.grad_y = torch.zeros_like(self.y)
-        self.idx1 = torch.zeros(b, n, dtype=torch.int32, device=self.device)
-        self.idx2 = torch.zeros(b, m, dtype=torch.int32, device=self.device)
+        self.dist1, self.dist2 = torch.zeros(b, n, **f32), torch.zeros(b, m, **f32)
+        self.idx1, self.idx2 = torch.zeros(b, n, **i32), torch.zeros(b, m, **i32)
+        self._gd1, self._gd2 = torch.zeros(b, n, **f32), torch.zeros(b, m, **f32)
+        self._ws = torch.empty(max(self.lib.nnd_workspace_bytes(b, n, m), 256), dtype=torch.uint8, device=dev)
+        self._rws = chamfer_reduce_workspace(dev)
         self.graph = None
         self.use_graph = use_graph
         self.replays = 0
 
-    # what one iteration computes (also the eager path when use_graph is False)
+    # what one iteration computes (also the eager path when use_graph is False): 3-4 forward launches, the fused
+    # mask + mean/mean reduction + d loss/d dist, 2 memsets + the gradient kernel -- all over static buffers
     def _body(self):
-        d1, d2, i1, i2 = nnd_forward_raw(self.x, self.y)
-        k1, k2 = d1 < self.trunc, d2 < self.trunc  # loss.py:151-154: distances >= trunc do not count
-        z1, z2 = torch.where(k1, d1, 0.0), torch.where(k2, d2, 0.0)
+        lib, st = self.lib, _stream_ptr(self.device)
+        b, n, m = self.b, self.n, self.m
+        rc = lib.nnd_forward_cuda_f32(self.x.data_ptr(), self.y.data_ptr(), b, n, m, self.dist1.data_ptr(),
+                                      self.dist2.data_ptr(), self.idx1.data_ptr(), self.idx2.data_ptr(),
+                                      self._ws.data_ptr(), self._ws.numel(), st)
+        _cabi.check(rc, "nnd_forward_cuda_f32")
         # point_reduction = mean (divide by the cloud length), batch_reduction = mean, both directions summed
-        self.loss.copy_((z1.sum(1) / self.n).sum() / self.b + (z2.sum(1) / self.m).sum() / self.b)
-        gd1 = k1.to(torch.float32) / (self.n * self.b)
-        gd2 = k2.to(torch.float32) / (self.m * self.b)
-        g1, g2 = nnd_backward_raw(self.x, self.y, gd1, gd2, i1, i2)
-        self.grad_x.copy_(g1)
-        self.grad_y.copy_(g2)
-        self.idx1.copy_(i1)
-        self.idx2.copy_(i2)
+        s1, s2 = 1.0 / (max(n, 1) * max(b, 1)), 1.0 / (max(m, 1) * max(b, 1))
+        rc = lib.nnd_chamfer_reduce_cuda_f32(self.dist1.data_ptr(), self.dist2.data_ptr(), b, n, m, self.trunc, s1, s2,
+                                             self.loss.data_ptr(), self._gd1.data_ptr(), self._gd2.data_ptr(),
+                                             self._rws.data_ptr(), self._rws.numel(), st)
+        _cabi.check(rc, "nnd_chamfer_reduce_cuda_f32")
+        rc = lib.nnd_backward_cuda_f32(self.x.data_ptr(), self.y.data_ptr(), self._gd1.data_ptr(), self._gd2.data_ptr(),
+                                       self.idx1.data_ptr(), self.idx2.data_ptr(), b, n, m, self.grad_x.data_ptr(),
+                                       self.grad_y.data_ptr(), st)
+        _cabi.check(rc, "nnd_backward_cuda_f32")
 
     def _capture(self):
         s = torch.cuda.Stream(self.device)
