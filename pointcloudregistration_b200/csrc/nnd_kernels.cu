@@ -255,8 +255,15 @@ __global__ void __launch_bounds__(256) nnd_finalize_kernel(FinParams p) {
         if (a1 == bq) found = 4 * s4 + 1;
         if (a0 == bq) found = 4 * s4;
       }
-      d.dist[g] = bq;
-      d.idx[g] = base + found;
+      // my_lib.cpp:16 accepts k == 0 unconditionally and later candidates only if d < best: a NaN first distance
+      // (NaN query, or NaN first target) is therefore the answer.  The scan's minimum ignores NaNs, which gives the
+      // reference's result in every other non-finite case.
+      const float* t0 = d.tsoa + (batch * d.ttiles * 3) * (long long)TT;
+      float first, unused;
+      upk2(sqdist2(pk2(t0[0], t0[0]), pk2(t0[TT], t0[TT]), pk2(t0[2 * TT], t0[2 * TT]), nqx, nqy, nqz, one), first, unused);
+      const bool nan0 = first != first;
+      d.dist[g] = nan0 ? first : bq;
+      d.idx[g] = nan0 ? 0 : base + found;
     }
   }
 }

@@ -272,7 +272,11 @@ __global__ void __launch_bounds__(256) nnd_finalize_cols_kernel(FinColParams p) 
     }
     long long j = j0 + found;
     j = j < p.n ? j : p.n - 1;
-    p.dist[g] = bq;
-    p.idx[g] = (int32_t)j;
+    // my_lib.cpp:16: the first candidate (row 0) is accepted unconditionally, so a NaN first distance is the answer
+    float first, unused;
+    upk2(sqdist2(TX, TY, TZ, pk2(-rows[0], -rows[0]), pk2(-rows[1], -rows[1]), pk2(-rows[2], -rows[2]), one), first, unused);
+    const bool nan0 = first != first;
+    p.dist[g] = nan0 ? first : bq;
+    p.idx[g] = nan0 ? 0 : (int32_t)j;
   }
 }

@@ -120,6 +120,34 @@ def test_nonfinite_inputs_do_not_hang(cuda_lib, device):
     assert np.array_equal(d1[0, ok1], g1[0, ok1]) and w1.shape[1] == 599
 
 
+def _same_with_nans(got, want):
+    gn, wn = np.isnan(got), np.isnan(want)
+    return np.array_equal(gn, wn) and got[~gn].tobytes() == want[~wn].tobytes()
+
+
+@pytest.mark.parametrize("n,m", [(600, 700), (8200, 8300)])  # two-pass path and symmetric path
+@pytest.mark.parametrize("first_too", [False, True])
+def test_nonfinite_inputs_follow_the_reference_rule(cuda_lib, device, n, m, first_too):
+    """my_lib.cpp:16 `if (k == 0 || d < best)`: NaN candidates are skipped unless they come first, +inf competes
+    normally.  Non-finite points in the middle of both clouds, and (first_too) at index 0 of either cloud."""
+    x1 = synthetic.uniform(2, n, 11).numpy()
+    x2 = synthetic.uniform(2, m, 12).numpy()
+    x1[0, 3] = np.nan
+    x1[1, n - 1, 2] = np.inf
+    x1[1, 17] = 3e19           # squares overflow to +inf
+    x2[0, 5] = np.inf
+    x2[0, 9, 1] = np.nan
+    x2[1, m // 2] = -np.inf
+    if first_too:
+        x1[0, 0, 1] = np.nan   # every column of batch 0 sees a NaN first candidate
+        x2[1, 0] = np.inf      # every row of batch 1 sees d(k=0) = +inf (or NaN for the inf rows)
+        x2[0, 0, 0] = np.nan
+    d1, d2, i1, i2 = gpu_forward(x1, x2, device)
+    w1, w2, j1, j2 = oracle.forward(x1, x2)
+    assert np.array_equal(i1, j1) and np.array_equal(i2, j2)
+    assert _same_with_nans(d1, w1) and _same_with_nans(d2, w2)
+
+
 def test_overflow_to_inf_keeps_index_zero(cuda_lib, device):
     q = np.zeros((1, 3, 3), np.float32)
     t = np.full((1, 40, 3), 3e19, np.float32)  # every squared distance overflows to +inf

@@ -42,6 +42,26 @@ def test_port_matches_compiled_reference(kind):
     assert bits_equal(pg[0], rg[0]) and bits_equal(pg[1], rg[1])
 
 
+@pytest.mark.skipif(not oracle.have_reference(), reason="oracle/_ref not built (needs /root/reference)")
+def test_port_matches_compiled_reference_on_nonfinite_inputs():
+    """my_lib.cpp:16 accepts k == 0 unconditionally: NaN sticks only when it comes first; +inf competes normally."""
+    x1 = synthetic.uniform(2, 300, 41).numpy()
+    x2 = synthetic.uniform(2, 200, 42).numpy()
+    x1[0, 3] = np.nan
+    x1[1, 0, 1] = np.nan
+    x1[1, 17] = 3e19
+    x2[0, 0] = np.inf
+    x2[0, 9, 1] = np.nan
+    x2[1, 100] = -np.inf
+    want = oracle.reference_forward(x1, x2)
+    got = oracle.forward(x1, x2)
+    for g, w in zip(got[2:], want[2:]):
+        assert np.array_equal(g, w)
+    for g, w in zip(got[:2], want[:2]):
+        assert np.array_equal(np.isnan(g), np.isnan(w)) and g[~np.isnan(g)].tobytes() == w[~np.isnan(w)].tobytes()
+    assert np.isnan(got[0]).any() and np.isinf(got[0]).any()
+
+
 def _dense(x1, x2):
     # (d0 + d1) + d2 with every op rounded to fp32, first-occurrence argmin: my_lib.cpp:12-19
     diff = x2[:, None, :, :] - x1[:, :, None, :]
