@@ -930,6 +930,18 @@ int nnd_backward_term_cuda_f32(const float* query, const float* target, const fl
   return launch_grad(gp, (cudaStream_t)stream);
 }
 
+#ifdef NND_SYM_COUNT
+int nnd_debug_sym_counters(unsigned long long* out2) {  // {slow-path entries, warp steps}; resets both
+  unsigned long long z = 0;
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(&out2[0], g_sym_slow, 8);
+  cudaMemcpyFromSymbol(&out2[1], g_sym_steps, 8);
+  cudaMemcpyToSymbol(g_sym_slow, &z, 8);
+  cudaMemcpyToSymbol(g_sym_steps, &z, 8);
+  return 0;
+}
+#endif
+
 size_t nnd_chamfer_reduce_workspace_bytes(void) { return (size_t)kReduceMaxBlocks * sizeof(double) + 256; }
 
 int nnd_chamfer_reduce_cuda_f32(const float* dist1, const float* dist2, int b, int n, int m, float trunc, float scale1,

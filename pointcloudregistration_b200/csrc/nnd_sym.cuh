@@ -44,6 +44,10 @@ struct FinColParams {
   float one;
 };
 
+#ifdef NND_SYM_COUNT  // dev instrumentation (tools/slow_path_rate.py): slow-path entries / 4-target warp steps
+__device__ unsigned long long g_sym_slow, g_sym_steps;
+#endif
+
 template <int TT>
 struct __align__(128) SymStage {
   float xyz[3 * TT];
@@ -209,9 +213,16 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
           const unsigned u0 = __float_as_uint(c0), u1 = __float_as_uint(c1);
           const unsigned u2 = __float_as_uint(c2), u3 = __float_as_uint(c3);
           const bool ev = (u0 <= h0) | (u1 <= h1) | (u2 <= h2) | (u3 <= h3);
-          if (__any_sync(FULL, ev))
+          if (__any_sync(FULL, ev)) {
+#ifdef NND_SYM_COUNT
+            if (lane == 0) atomicAdd(&g_sym_slow, 1ull);
+#endif
             sym_column_update(u0, u1, u2, u3, h0, h1, h2, h3, lane, group, ckeys, cdist, filt, tile * TT, koff);
+          }
         }
+#ifdef NND_SYM_COUNT
+        if (lane == 0) atomicAdd(&g_sym_steps, (unsigned long long)(C / 4));
+#endif
         const int cbase = tile * TT + ch * C;
 #pragma unroll
         for (int q = 0; q < QPT; ++q) {
