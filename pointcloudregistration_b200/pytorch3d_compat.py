@@ -25,6 +25,7 @@ import torch
 from torch.autograd import Function
 
 from . import _cabi
+from . import functional as F_
 from .functional import _check_clouds, _stream_ptr, nnd_backward_raw, nnd_forward_raw, nnd_query_raw
 
 _KNN = namedtuple("KNN", "dists idx knn")
@@ -212,6 +213,35 @@ def _full_lengths(points, lengths):
     return lengths.to(device=points.device, dtype=torch.int64)
 
 
+_reduce_ws = {}  # (device, stream) -> zeroed scratch of the fused epilogue (the kernel hands it back zeroed)
+
+
+class _FusedChamferFunction(Function):
+    """Dense, unweighted chamfer with scalar output: nnd forward + ONE fused launch for mask, both reductions and
+    d loss/d dist (nnd_chamfer_reduce_cuda_f32); the backward scales the saved d loss/d dist and runs nnd's backward.
+    Same arithmetic as the general path below up to the summation order (float64 partial sums here)."""
+
+    @staticmethod
+    def forward(ctx, x, y, trunc, s1, s2):
+        xc, yc = x.detach().contiguous(), y.detach().contiguous()  # dtype/device checked by nnd_forward_raw
+        d1, d2, i1, i2 = F_.nnd_forward_raw(xc, yc)
+        key = (xc.device, torch.cuda.current_stream(xc.device).cuda_stream)
+        ws = _reduce_ws.get(key)
+        if ws is None:
+            ws = _reduce_ws[key] = F_.chamfer_reduce_workspace(xc.device)
+        loss = torch.empty((), dtype=torch.float32, device=xc.device)
+        gd1, gd2 = torch.empty_like(d1), torch.empty_like(d2)
+        F_.chamfer_reduce_raw(d1, d2, trunc, s1, s2, loss, gd1, gd2, ws)
+        ctx.save_for_backward(xc, yc, gd1, gd2, i1, i2)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        xc, yc, gd1, gd2, i1, i2 = ctx.saved_tensors
+        gx, gy = F_.nnd_backward_raw(xc, yc, gd1 * g, gd2 * g, i1, i2)
+        return gx, gy, None, None, None
+
+
 def _chamfer(x, y, x_lengths, y_lengths, x_normals, y_normals, weights, trunc, batch_reduction, point_reduction):
     _validate(batch_reduction, point_reduction)
     if x.ndim != 3 or y.ndim != 3:
@@ -228,6 +258,14 @@ def _chamfer(x, y, x_lengths, y_lengths, x_normals, y_normals, weights, trunc, b
         if weights.sum() == 0.0:  # loss.py:128-135
             z = (x.sum((1, 2)) * weights.view(n)) * 0.0
             return (z.sum(), z.sum()) if batch_reduction in ["mean", "sum"] else (z, z)
+    if (weights is None and x_lengths is None and y_lengths is None and batch_reduction is not None
+            and (x_normals is None or y_normals is None) and n > 0 and p1 > 0 and p2 > 0 and d == 3):
+        _check_k_d(x, y, 1)
+        bdiv = n if batch_reduction == "mean" else 1
+        s1 = 1.0 / ((p1 if point_reduction == "mean" else 1) * bdiv)
+        s2 = 1.0 / ((p2 if point_reduction == "mean" else 1) * bdiv)
+        # no truncation = a NaN threshold: `dist >= NaN` is never true, so nothing is dropped (not even +inf)
+        return _FusedChamferFunction.apply(x, y, float("nan") if trunc is None else float(trunc), s1, s2), None
     xl, yl = _full_lengths(x, x_lengths), _full_lengths(y, y_lengths)
     cham_x, cham_y, idx_x, idx_y = _nnd2(x, y, x_lengths, y_lengths)
     x_mask = torch.arange(p1, device=x.device)[None] >= xl[:, None]  # loss.py:113-118

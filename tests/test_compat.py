@@ -100,6 +100,8 @@ def test_knn_points_matches_oracle_both_layouts(cuda_lib, device):
     (None, False, False, "mean", "mean"),      # dip/train.py:84
     (1e9, False, False, "mean", "mean"),       # registration.py:236 (trunc=1e9)
     (0.002, False, False, "mean", "mean"),     # real truncation
+    (0.002, False, False, "sum", "mean"),      # fused epilogue, other scale combinations
+    (None, False, False, "mean", "sum"),
     (0.002, True, True, "sum", "sum"),
     (None, True, False, None, "mean"),
 ])
