@@ -113,6 +113,15 @@ int nnd_backward_cuda_f32(const float *xyz1, const float *xyz2,
                           int b, int n, int m,
                           float *gradxyz1, float *gradxyz2, void *stream);
 
+/* Tuning knob.  The symmetric forward has two scan kernels: the persistent TMA-fed one and, for row ranges of at least
+ * this many rows, the "panel" one that keeps the column points in uniform registers (one launch per panel of columns,
+ * DESIGN.md section 4.0).  Results are bit-identical.  Sets the threshold (rows > 0) and returns the previous value;
+ * rows <= 0 only queries.  Default 400000, or the environment variable NND_B200_PANEL_MIN_ROWS. */
+long long nnd_set_panel_min_rows(long long rows);
+/* Column tiles (512 points) per panel launch: 0 = chosen from the row count (default), 1, 2 or 4 = forced.  Returns the
+ * previous setting; other values only query.  Environment: NND_B200_PANEL_TILES. */
+int nnd_set_panel_tiles(int tiles);
+
 /* Fused truncated-chamfer epilogue (c2p-net/deformationpyramid/model/loss.py:150-215 with mean/mean reductions, the
  * form registration.py:236 uses):  loss[0] = scale1 * sum(dist1 < trunc ? dist1 : 0) + scale2 * sum(dist2 < trunc ? dist2 : 0),
  * and, when the pointers are non-null, graddist1[i] = dist1[i] < trunc ? scale1 : 0 (likewise graddist2): d loss / d dist,

@@ -7,7 +7,7 @@ or PyTorch fallback.
 from __future__ import annotations
 
 import ctypes
-from ctypes import c_char_p, c_float, c_int, c_size_t, c_void_p
+from ctypes import c_char_p, c_float, c_int, c_longlong, c_size_t, c_void_p
 from pathlib import Path
 
 import os
@@ -40,6 +40,8 @@ SIGNATURES = {
     "nnd_backward_term_cuda_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p,
                                             c_void_p, c_void_p]),
     "nnd_last_launch_count": (c_int, []),
+    "nnd_set_panel_min_rows": (c_longlong, [c_longlong]),
+    "nnd_set_panel_tiles": (c_int, [c_int]),
     "nnd_chamfer_reduce_workspace_bytes": (c_size_t, []),
     "nnd_chamfer_reduce_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float, c_float, c_void_p,
                                              c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),

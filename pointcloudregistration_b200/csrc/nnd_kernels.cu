@@ -39,6 +39,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "nnd_b200.h"
 
 #define NND_VERSION_STRING "nnd_b200 0.1.0 sm_100a"
@@ -242,7 +244,7 @@ __global__ void __launch_bounds__(256) nnd_finalize_kernel(FinParams p) {
       const ulonglong2* cy = reinterpret_cast<const ulonglong2*>(sx + TT);
       const ulonglong2* cz = reinterpret_cast<const ulonglong2*>(sx + 2 * TT);
       int found = 0;
-#pragma unroll
+#pragma unroll 8
       for (int s4 = C / 4 - 1; s4 >= 0; --s4) {  // descending: the last hit is the lowest k
         const ulonglong2 X = __ldg(cx + s4), Y = __ldg(cy + s4), Z = __ldg(cz + s4);
         const uint64_t d0 = sqdist2(X.x, Y.x, Z.x, nqx, nqy, nqz, one);
@@ -417,6 +419,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
 }
 
 #include "nnd_sym.cuh"
+#include "nnd_symc.cuh"
 
 // ----------------------------------------------------------------------------------
 // backward
@@ -553,6 +556,100 @@ int launch_sym(const SymParams& yp, int grid, size_t smem, cudaStream_t st) {
   return 0;
 }
 
+// ---- panel path (nnd_symc.cuh): one launch per panel of 1, 2 or 4 target tiles, rotating over 8, 4 or 2 internal
+// streams / constant buffers.  The caller's stream forks into them and joins them at the end, so the whole thing is
+// ordered like a single operation on `st` (also under stream capture).
+struct PanelCtx {
+  cudaStream_t s[kPanelMaxBufs] = {};
+  cudaEvent_t fork = nullptr, join[kPanelMaxBufs] = {};
+  bool ready = false;
+};
+std::mutex g_panel_mu;  // the constant window is per device: panel scans of one process are enqueued one at a time
+
+int panel_ctx(PanelCtx** out) {
+  static PanelCtx ctx[64];
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  PanelCtx& c = ctx[dev & 63];
+  if (!c.ready) {
+    for (int i = 0; i < kPanelMaxBufs; ++i) {
+      if ((e = cudaStreamCreateWithFlags(&c.s[i], cudaStreamNonBlocking)) != cudaSuccess) return (int)e;
+      if ((e = cudaEventCreateWithFlags(&c.join[i], cudaEventDisableTiming)) != cudaSuccess) return (int)e;
+    }
+    if ((e = cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming)) != cudaSuccess) return (int)e;
+    c.ready = true;
+  }
+  *out = &c;
+  return 0;
+}
+
+// Rows per launch below which the panel path does not pay (each launch must be long against its launch, copy and
+// ramp): NND_B200_PANEL_MIN_ROWS overrides (tests use 1 to push every symmetric scan through the panels).
+long long g_panel_min_rows = -1;
+int g_panel_tiles = -1;  // 0 = choose from the row count; 1, 2, 4 = forced (tests, tuning)
+long long panel_min_rows() {
+  if (g_panel_min_rows < 0) {
+    const char* e = getenv("NND_B200_PANEL_MIN_ROWS");
+    g_panel_min_rows = e ? atoll(e) : 400000;
+    if (g_panel_min_rows < 1) g_panel_min_rows = 1;
+  }
+  return g_panel_min_rows;
+}
+
+template <int PT>
+int scan_panels_pt(SymCParams yp, const float* soa2, int b, int qblocks, PanelCtx* c) {
+  constexpr int THREADS = kThreads, QPT = kQPT;
+  constexpr int NBUF = 8 / PT;
+  const size_t smem = (size_t)PT * kTT * sizeof(unsigned) + (size_t)THREADS * QPT * 8;
+  cudaError_t e;
+  int turn = 0;
+  for (int batch = 0; batch < b; ++batch) {
+    for (int tile_lo = 0; tile_lo < yp.ttiles; tile_lo += PT, ++turn) {
+      const int which = turn % NBUF;
+      yp.batch = batch;
+      yp.tile_lo = tile_lo;
+      yp.ntiles = yp.ttiles - tile_lo < PT ? yp.ttiles - tile_lo : PT;
+      yp.cofs = which * PT * 3 * kTT;
+      const float* src = soa2 + ((long long)batch * yp.ttiles + tile_lo) * (3 * kTT);
+      e = cudaMemcpyToSymbolAsync(c_panel, src, sizeof(float) * yp.ntiles * 3 * kTT, sizeof(float) * yp.cofs,
+                                  cudaMemcpyDeviceToDevice, c->s[which]);
+      if (e != cudaSuccess) return (int)e;
+      const bool full = yp.ntiles == PT && (tile_lo + PT) * kTT <= yp.m;
+      if (full)
+        nnd_scan_symc_kernel<THREADS, QPT, kTT, kChunk, kMinBlocks, PT, true><<<qblocks, THREADS, smem, c->s[which]>>>(yp);
+      else
+        nnd_scan_symc_kernel<THREADS, QPT, kTT, kChunk, kMinBlocks, PT, false><<<qblocks, THREADS, smem, c->s[which]>>>(yp);
+      ++g_launches;
+    }
+  }
+  return 0;
+}
+
+int scan_panels(const SymCParams& yp, const float* soa2, int b, int qblocks, int sms, cudaStream_t st) {
+  std::lock_guard<std::mutex> lock(g_panel_mu);
+  PanelCtx* c = nullptr;
+  int rc = panel_ctx(&c);
+  if (rc) return rc;
+  cudaError_t e;
+  if ((e = cudaEventRecord(c->fork, st)) != cudaSuccess) return (int)e;
+  for (int i = 0; i < kPanelMaxBufs; ++i)
+    if ((e = cudaStreamWaitEvent(c->s[i], c->fork, 0)) != cudaSuccess) return (int)e;
+  // launches in flight x CTAs per launch should cover the 2 * sms resident CTAs about twice
+  if (g_panel_tiles < 0) g_panel_tiles = getenv("NND_B200_PANEL_TILES") ? atoi(getenv("NND_B200_PANEL_TILES")) : 0;
+  int pt = qblocks * 2 >= 3 * sms ? 4 : qblocks * 4 >= 3 * sms ? 2 : 1;
+  if (g_panel_tiles == 1 || g_panel_tiles == 2 || g_panel_tiles == 4) pt = g_panel_tiles;
+  rc = pt == 4 ? scan_panels_pt<4>(yp, soa2, b, qblocks, c)
+     : pt == 2 ? scan_panels_pt<2>(yp, soa2, b, qblocks, c)
+               : scan_panels_pt<1>(yp, soa2, b, qblocks, c);
+  if (rc) return rc;
+  for (int i = 0; i < kPanelMaxBufs; ++i) {
+    if ((e = cudaEventRecord(c->join[i], c->s[i])) != cudaSuccess) return (int)e;
+    if ((e = cudaStreamWaitEvent(st, c->join[i], 0)) != cudaSuccess) return (int)e;
+  }
+  return check_last(cudaGetLastError());
+}
+
 template <int THREADS, int QPT, int MINB>
 void launch_scan(const ScanParams& sp, int grid, cudaStream_t st) {
   nnd_scan_kernel<THREADS, QPT, kTT, kChunk, kStages, MINB><<<grid, THREADS, 0, st>>>(sp);
@@ -635,14 +732,41 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   yp.one = 1.0f;
   const int grid_full = di.sms * si.minb;
   const int grid = yp.total_units < grid_full ? (int)yp.total_units : grid_full;
-  const size_t smem = sizeof(SymStage<kTT>) * kStages;
+  const size_t smem = sizeof(SymStage<kTT>) * kStages + (NND_SYM_LAZY ? (size_t)si.threads * si.qpt * 8 : 0);
+  if (shape == kShapeLarge && NND_SYM_LAZY == kChunk && nrows >= panel_min_rows()) {
+    SymCParams cp{};
+    cp.qsoa = soa1;
+    cp.rkeys = rkeys;
+    cp.ckeys = colkeys;
+    cp.cdist = cdist;
+    cp.n = n1;
+    cp.m = n2;
+    cp.row_lo = row_lo;
+    cp.row_hi = row_hi;
+    cp.qtiles = yp.qtiles;
+    cp.ttiles = yp.ttiles;
+    cp.one = 1.0f;
+    {  // seed the column filter from whole sample tiles of rows inside [row_lo, row_hi): ~0.2-0.4 % of the scan
+      const int t_first = (row_lo + kTT - 1) / kTT;
+      int ns = row_hi / kTT - t_first;
+      const int want = nrows >= 500000 ? 4 : nrows >= 200000 ? 2 : 1;
+      ns = ns > want ? want : ns;
+      static const int dbg_noseed = getenv("NND_B200_PANEL_NOSEED") ? 1 : 0;  // diagnosis only
+      if (ns > 0 && !dbg_noseed) {
+        dim3 g((unsigned)((n2 + 511) / 512), (unsigned)b);
+        nnd_seed_filter_kernel<kTT><<<g, 256, 0, st>>>(c2, soa1, cdist, n2, yp.ttiles, yp.qtiles, t_first, ns, 1.0f);
+        ++g_launches;
+      }
+    }
+    rc = scan_panels(cp, soa2, b, yp.qblocks, di.sms, st);
+  } else
   switch (shape) {
     case kShapeLarge: rc = launch_sym<kThreads, kQPT, kMinBlocks>(yp, grid, smem, st); break;
     case kShapeMid: rc = launch_sym<256, 2, 4>(yp, grid, smem, st); break;
     default: rc = launch_sym<128, 2, 8>(yp, grid, smem, st); break;
   }
   if (rc) return rc;
-  ++g_launches;
+  if (!(shape == kShapeLarge && NND_SYM_LAZY == kChunk && nrows >= panel_min_rows())) ++g_launches;
   if (ev) cudaEventRecord(ev[2], st);
   debug_sync("scan_sym", st);
 
@@ -650,7 +774,7 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   fp.ndir = 1;
   fp.one = 1.0f;
   fp.d[0] = FinDir{rkeys, c1, soa2, dist1, idx1, n1, tiles_of(n2), row_lo, nrows, (long long)b * nrows};
-  nnd_finalize_kernel<kTT, kChunk><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
+  nnd_finalize_kernel<kTT, (NND_SYM_LAZY ? NND_SYM_LAZY : kChunk)><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
   ++g_launches;
   if (ev) cudaEventRecord(ev[3], st);
   debug_sync("finalize_rows", st);
@@ -941,6 +1065,18 @@ int nnd_debug_sym_counters(unsigned long long* out2) {  // {slow-path entries, w
   return 0;
 }
 #endif
+
+long long nnd_set_panel_min_rows(long long rows) {
+  const long long before = panel_min_rows();
+  if (rows > 0) g_panel_min_rows = rows;
+  return before;
+}
+
+int nnd_set_panel_tiles(int tiles) {
+  const int before = g_panel_tiles < 0 ? 0 : g_panel_tiles;
+  if (tiles == 0 || tiles == 1 || tiles == 2 || tiles == 4) g_panel_tiles = tiles;
+  return before;
+}
 
 size_t nnd_chamfer_reduce_workspace_bytes(void) { return (size_t)kReduceMaxBlocks * sizeof(double) + 256; }
 

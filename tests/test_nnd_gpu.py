@@ -283,6 +283,73 @@ def test_aten_shim_writes_in_place(cuda_lib, device):
         my_lib.nnd_forward_cuda(a[:, ::2], b, dist1, dist2, idx1, idx2)  # my_lib_cuda.cpp:5
 
 
+# ---------------------------------------------------------------- the panel scan (columns in uniform registers)
+@pytest.fixture
+def panels_forced(cuda_lib):
+    """Push every symmetric scan through nnd_scan_symc_kernel (normally only row ranges >= 400 000 rows)."""
+    before = cuda_lib.nnd_set_panel_min_rows(1)
+    yield
+    cuda_lib.nnd_set_panel_min_rows(before)
+
+
+@pytest.mark.parametrize("kind,b,n,m", [
+    ("uniform", 1, 8192, 8192),        # exactly 4 panels of 4 tiles
+    ("uniform", 2, 9001, 10241),       # ragged rows, ragged last panel (21 tiles), two batch elements
+    ("clustered", 1, 20000, 8200),     # last panel = 1 tile + 8 points
+    ("lattice", 1, 12000, 12345),      # exact ties everywhere: lowest index must win through the panels too
+    ("identical", 1, 9000, 9000),
+    ("crosscopy", 3, 8192, 16000),
+])
+def test_panel_scan_matches_oracle(panels_forced, cuda_lib, device, kind, b, n, m):
+    x1, x2 = synthetic.make_pair(kind, b, n, m, 43)
+    want = oracle.forward(x1.numpy(), x2.numpy(), threads=8)
+    assert cuda_lib.nnd_forward_is_symmetric(n, m)
+    got = gpu_forward(x1, x2, device)
+    assert_forward_exact(got, want, what=f"panel {kind}: ")
+    assert cuda_lib.nnd_last_launch_count() >= 3 + (m + 2047) // 2048 * b  # one launch per panel (at most 4 tiles) at least
+
+
+@pytest.mark.parametrize("tiles", [1, 2, 4])
+def test_panel_scan_equals_persistent_scan_bitwise(cuda_lib, device, tiles):
+    """Same inputs through both scan kernels: all four outputs identical bit for bit (262144 points, clustered)."""
+    x1, x2 = synthetic.make_pair("clustered", 1, 262144, 200000, 44)
+    before = cuda_lib.nnd_set_panel_min_rows(1 << 40)
+    try:
+        ref = gpu_forward(x1, x2, device)
+        cuda_lib.nnd_set_panel_min_rows(1)
+        cuda_lib.nnd_set_panel_tiles(tiles)
+        got = gpu_forward(x1, x2, device)
+        assert cuda_lib.nnd_last_launch_count() >= 200000 // (512 * tiles)
+    finally:
+        cuda_lib.nnd_set_panel_min_rows(before)
+        cuda_lib.nnd_set_panel_tiles(0)
+    for a, c in zip(got, ref):
+        assert a.tobytes() == c.tobytes()
+
+
+def test_panel_scan_under_graph_capture_and_side_stream(panels_forced, cuda_lib, device):
+    """The panel path forks into internal streams and joins back: it must behave like one operation on the caller's
+    stream, also while that stream is being captured into a CUDA graph."""
+    x1, x2 = synthetic.make_pair("uniform", 1, 10000, 9000, 45)
+    want = oracle.forward(x1.numpy(), x2.numpy(), threads=8)
+    a, c = x1.to(device), x2.to(device)
+    s = torch.cuda.Stream(device=device)
+    with torch.cuda.stream(s):
+        out = F.nnd_forward_raw(a, c)
+    s.synchronize()
+    assert_forward_exact(tuple(t.cpu().numpy() for t in out), want, what="side stream: ")
+    g = torch.cuda.CUDAGraph()
+    static_a = a.clone()
+    torch.cuda.synchronize()
+    with torch.cuda.graph(g):
+        cap = F.nnd_forward_raw(static_a, c)
+    static_a.copy_(a.flip(1))  # new rows, replay must see them
+    g.replay()
+    torch.cuda.synchronize()
+    want2 = oracle.forward(x1.flip(1).contiguous().numpy(), x2.numpy(), threads=8)
+    assert_forward_exact(tuple(t.cpu().numpy() for t in cap), want2, what="graph replay: ")
+
+
 def test_non_contiguous_inputs_and_side_stream(cuda_lib, device):
     import torch_nndistance as NND
 
