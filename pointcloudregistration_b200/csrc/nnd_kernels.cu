@@ -160,12 +160,13 @@ struct PrepCloud {
   float* soa;        // [b][tiles][3][TT]
   int n, tiles;
   long long padded_total;  // b * tiles * TT
+  long long src_stride;    // points between batch elements of src (n, or more when src is a row range of a cloud)
 };
 struct PrepParams {
   PrepCloud c[2];
   int nclouds;
-  unsigned long long* fill64[2];  // key arrays set to kKeyInit
-  long long count64[2];
+  unsigned long long* fill64[3];  // key arrays set to kKeyInit
+  long long count64[3];
   unsigned* fill32;  // column filter set to 0xffffffff
   long long count32;
 };
@@ -183,6 +184,12 @@ struct FinDir {
   int nq, ttiles;
   int row_lo, nrows;  // rows [row_lo, row_lo + nrows) of every batch element are finalized
   long long count;    // b * nrows
+  // Partial results instead of dist/idx (role-swapped row ranges): keyout[batch * key_stride + row] =
+  // (dist_bits << 32 | (idx_offset + idx) / key_group), the column-key format of nnd_sym.cuh.  No NaN-first rule here:
+  // it is applied once, after the partial keys of all ranges have been merged (nnd_finalize_cols_kernel).
+  unsigned long long* keyout;
+  long long key_stride;
+  int idx_offset, key_group;
 };
 struct FinParams {
   FinDir d[2];
@@ -205,7 +212,7 @@ __global__ void __launch_bounds__(256) nnd_prepare_kernel(PrepParams p) {
       const int j = (int)(g - batch * per_batch);
       const int tile = j / TT, off = j - tile * TT;
       const int js = j < c.n ? j : c.n - 1;  // pad by repeating the last point
-      const float* s = c.src + (batch * c.n + js) * 3;
+      const float* s = c.src + (batch * c.src_stride + js) * 3;
       float* d = c.soa + ((batch * c.tiles + tile) * 3) * (long long)TT + off;
       d[0] = s[0];
       d[TT] = s[1];
@@ -213,7 +220,7 @@ __global__ void __launch_bounds__(256) nnd_prepare_kernel(PrepParams p) {
     }
   }
 #pragma unroll
-  for (int k = 0; k < 2; ++k)
+  for (int k = 0; k < 3; ++k)
     for (long long g = first; g < p.count64[k]; g += stride) p.fill64[k][g] = kKeyInit;
   for (long long g = first; g < p.count32; g += stride) p.fill32[g] = 0xffffffffu;
 }
@@ -264,8 +271,13 @@ __global__ void __launch_bounds__(256) nnd_finalize_kernel(FinParams p) {
       float first, unused;
       upk2(sqdist2(pk2(t0[0], t0[0]), pk2(t0[TT], t0[TT]), pk2(t0[2 * TT], t0[2 * TT]), nqx, nqy, nqz, one), first, unused);
       const bool nan0 = first != first;
-      d.dist[g] = nan0 ? first : bq;
-      d.idx[g] = nan0 ? 0 : base + found;
+      if (d.keyout != nullptr) {
+        d.keyout[batch * d.key_stride + d.row_lo + (w - batch * d.nrows)] =
+            (key & 0xffffffff00000000ull) | (unsigned long long)(unsigned)((d.idx_offset + base + found) / d.key_group);
+      } else {
+        d.dist[g] = nan0 ? first : bq;
+        d.idx[g] = nan0 ? 0 : base + found;
+      }
     }
   }
 }
@@ -516,6 +528,14 @@ inline size_t colkey_count(int b, int m) { return (size_t)b * tiles_of(m) * kTT;
 inline size_t colkey_bytes(int b, int m) { return align_up(colkey_count(b, m) * sizeof(unsigned long long), 256); }
 inline size_t filter_bytes(int b, int m) { return align_up(colkey_count(b, m) * sizeof(unsigned), 256); }
 
+// Workspace of the row-range forward: SoA copies of both clouds plus either orientation's keys and filter
+// (normal: row keys of xyz1 + filter of xyz2; role-swapped: row keys of xyz2 + column keys and filter of xyz1's range).
+inline size_t rows_need(int b, int n, int m) {
+  const size_t normal = key_bytes(b, n) + filter_bytes(b, m);
+  const size_t swapped = key_bytes(b, m) + colkey_bytes(b, n) + filter_bytes(b, n);
+  return soa_bytes(b, n) + soa_bytes(b, m) + (normal > swapped ? normal : swapped);
+}
+
 int check_last(cudaError_t e) { return e == cudaSuccess ? 0 : (int)e; }
 
 constexpr int kReduceMaxBlocks = 1024;  // partial sums of nnd_chamfer_reduce_kernel
@@ -597,6 +617,9 @@ long long panel_min_rows() {
   return g_panel_min_rows;
 }
 
+// Shortest row range that takes the role-swapped panel path (each panel launch streams <= 2048 of its rows).
+long long panel_swap_min_rows() { return panel_min_rows() < 8192 ? panel_min_rows() : 8192; }
+
 template <int PT>
 int scan_panels_pt(SymCParams yp, const float* soa2, int b, int qblocks, PanelCtx* c) {
   constexpr int THREADS = kThreads, QPT = kQPT;
@@ -662,6 +685,97 @@ inline ScanShape sym_shape(int b, int n, int m, int sms) {
   return use_symmetric(n, m) ? kShapeLarge : choose_shape(b, n, m, sms);
 }
 
+int scan_panels(const SymCParams& yp, const float* soa2, int b, int qblocks, int sms, cudaStream_t st);
+
+// Role-swapped row range: when the range [row_lo, row_hi) of xyz1 is shorter than xyz2 (a rank's shard of the
+// multi-GPU path, or simply n < m), the panel scan runs with xyz2 in the registers and the RANGE as the streamed
+// columns: every launch then has ceil(m / 2048) CTAs however short the range is, and each column sees m / 256 warp
+// visits, so the slow path stays rare.  The kernel's row direction (xyz2 points -> nearest range row) is finalized
+// to exact indices and written out as column keys in the usual format (dist_bits << 32 | xyz1 row / 8); its column
+// direction (range rows -> nearest xyz2 point) is complete, because every range row has seen all of xyz2, and goes
+// straight to dist1 / idx1.
+int forward_rows_swapped_impl(const float* c1, int n1, const float* c2, int n2, int b, int row_lo, int row_hi,
+                              float* dist1, int32_t* idx1, unsigned long long* colkeys, void* workspace,
+                              const DeviceInfo& di, cudaEvent_t* ev, cudaStream_t st) {
+  const int nrows = row_hi - row_lo;
+  char* w = (char*)workspace;
+  float* soaR = (float*)w;  // xyz2: the register side
+  w += soa_bytes(b, n2);
+  float* soaS = (float*)w;  // rows [row_lo, row_hi) of xyz1 as a cloud of its own: the streamed side
+  w += soa_bytes(b, n1);
+  unsigned long long* keysR = (unsigned long long*)w;
+  w += key_bytes(b, n2);
+  unsigned long long* ckeysS = (unsigned long long*)w;
+  w += colkey_bytes(b, nrows);
+  unsigned* cdistS = (unsigned*)w;
+  const float* sub = c1 + (long long)row_lo * 3;
+
+  PrepParams pp{};
+  pp.nclouds = 2;
+  pp.c[0] = PrepCloud{c2, soaR, n2, tiles_of(n2), (long long)b * tiles_of(n2) * kTT, n2};
+  pp.c[1] = PrepCloud{sub, soaS, nrows, tiles_of(nrows), (long long)b * tiles_of(nrows) * kTT, n1};
+  pp.fill64[0] = keysR;
+  pp.count64[0] = (long long)b * n2;
+  pp.fill64[1] = ckeysS;
+  pp.count64[1] = (long long)colkey_count(b, nrows);
+  pp.fill64[2] = colkeys;  // padding entries of the output stay at the initial value
+  pp.count64[2] = (long long)colkey_count(b, n2);
+  pp.fill32 = cdistS;
+  pp.count32 = (long long)colkey_count(b, nrows);
+  {
+    long long total = pp.c[0].padded_total > pp.count64[2] ? pp.c[0].padded_total : pp.count64[2];
+    if (ev) cudaEventRecord(ev[0], st);
+    nnd_prepare_kernel<kTT><<<grid_for(total, di.sms), 256, 0, st>>>(pp);
+    ++g_launches;
+    if (ev) cudaEventRecord(ev[1], st);
+    debug_sync("prepare(swapped)", st);
+  }
+  const int qblocks = (n2 + kThreads * kQPT - 1) / (kThreads * kQPT);
+  {  // seed the filter of the range's points from whole sample tiles of xyz2
+    int ns = n2 / kTT;
+    const int want = n2 >= 500000 ? 4 : n2 >= 200000 ? 2 : 1;
+    ns = ns > want ? want : ns;
+    if (ns > 0) {
+      dim3 g((unsigned)((nrows + 511) / 512), (unsigned)b);
+      nnd_seed_filter_kernel<kTT><<<g, 256, 0, st>>>(sub, soaR, cdistS, nrows, tiles_of(nrows), tiles_of(n2), 0, ns, 1.0f, n1);
+      ++g_launches;
+    }
+  }
+  SymCParams cp{};
+  cp.qsoa = soaR;
+  cp.rkeys = keysR;
+  cp.ckeys = ckeysS;
+  cp.cdist = cdistS;
+  cp.n = n2;
+  cp.m = nrows;
+  cp.row_lo = 0;
+  cp.row_hi = n2;
+  cp.qtiles = tiles_of(n2);
+  cp.ttiles = tiles_of(nrows);
+  cp.one = 1.0f;
+  int rc = scan_panels(cp, soaS, b, qblocks, di.sms, st);
+  if (rc) return rc;
+  if (ev) cudaEventRecord(ev[2], st);
+  debug_sync("scan_panels(swapped)", st);
+
+  // xyz2 points -> exact nearest row of the range -> column keys
+  FinParams fp{};
+  fp.ndir = 1;
+  fp.one = 1.0f;
+  fp.d[0] = FinDir{keysR, c2, soaS, nullptr, nullptr, n2, tiles_of(nrows), 0, n2, (long long)b * n2,
+                   colkeys, (long long)tiles_of(n2) * kTT, row_lo,
+                   kShapes[sym_shape(b, n1, n2, di.sms)].qpt};  // the row-group size finalize_cols_impl will assume
+  nnd_finalize_kernel<kTT, kChunk><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
+  ++g_launches;
+  // range rows -> nearest xyz2 point (complete): dist1 / idx1 of rows [row_lo, row_hi)
+  FinColParams fc{ckeysS, c2, c1, dist1, idx1, n2, nrows, tiles_of(nrows), (long long)b * nrows, 1.0f, n1, row_lo};
+  nnd_finalize_cols_kernel<kTT, kQPT><<<grid_for(fc.count, di.sms), 256, 0, st>>>(fc);
+  ++g_launches;
+  if (ev) cudaEventRecord(ev[3], st);
+  debug_sync("finalize(swapped)", st);
+  return check_last(cudaGetLastError());
+}
+
 // Symmetric forward over the row range [row_lo, row_hi) of xyz1 (every batch element):
 //   prepare (SoA copies, key/filter init) -> nnd_scan_sym_kernel -> nnd_finalize_kernel for those rows.
 // colkeys receives this launch's column keys; finalize_cols_impl turns (merged) column keys into dist2/idx2.
@@ -674,8 +788,11 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   int rc = device_info(&di);
   if (rc) return rc;
   if (((uintptr_t)workspace & 255u) != 0) return NND_EWORKSPACE;
-  const size_t need = soa_bytes(b, n1) + soa_bytes(b, n2) + key_bytes(b, n1) + filter_bytes(b, n2);
+  const size_t need = rows_need(b, n1, n2);
   if (workspace_bytes < need) return NND_EWORKSPACE;
+  if (row_hi - row_lo > 0 && row_hi - row_lo < n2 && n2 >= panel_min_rows() && n2 >= 2 * kTT &&
+      row_hi - row_lo >= panel_swap_min_rows())
+    return forward_rows_swapped_impl(c1, n1, c2, n2, b, row_lo, row_hi, dist1, idx1, colkeys, workspace, di, ev, st);
   char* w = (char*)workspace;
   float* soa1 = (float*)w;
   w += soa_bytes(b, n1);
@@ -688,8 +805,8 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
 
   PrepParams pp{};
   pp.nclouds = nrows > 0 ? 2 : 0;
-  pp.c[0] = PrepCloud{c1, soa1, n1, tiles_of(n1), (long long)b * tiles_of(n1) * kTT};
-  pp.c[1] = PrepCloud{c2, soa2, n2, tiles_of(n2), (long long)b * tiles_of(n2) * kTT};
+  pp.c[0] = PrepCloud{c1, soa1, n1, tiles_of(n1), (long long)b * tiles_of(n1) * kTT, n1};
+  pp.c[1] = PrepCloud{c2, soa2, n2, tiles_of(n2), (long long)b * tiles_of(n2) * kTT, n2};
   pp.fill64[0] = rkeys;
   pp.count64[0] = nrows > 0 ? (long long)b * n1 : 0;
   pp.fill64[1] = colkeys;
@@ -754,7 +871,7 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
       static const int dbg_noseed = getenv("NND_B200_PANEL_NOSEED") ? 1 : 0;  // diagnosis only
       if (ns > 0 && !dbg_noseed) {
         dim3 g((unsigned)((n2 + 511) / 512), (unsigned)b);
-        nnd_seed_filter_kernel<kTT><<<g, 256, 0, st>>>(c2, soa1, cdist, n2, yp.ttiles, yp.qtiles, t_first, ns, 1.0f);
+        nnd_seed_filter_kernel<kTT><<<g, 256, 0, st>>>(c2, soa1, cdist, n2, yp.ttiles, yp.qtiles, t_first, ns, 1.0f, n2);
         ++g_launches;
       }
     }
@@ -786,7 +903,7 @@ int finalize_cols_impl(const float* c1, int n1, const float* c2, int n2, int b, 
   DeviceInfo di;
   int rc = device_info(&di);
   if (rc) return rc;
-  FinColParams cp{colkeys, c1, c2, dist2, idx2, n1, n2, tiles_of(n2), (long long)b * n2, 1.0f};
+  FinColParams cp{colkeys, c1, c2, dist2, idx2, n1, n2, tiles_of(n2), (long long)b * n2, 1.0f, n2, 0};
   if (kShapes[sym_shape(b, n1, n2, di.sms)].qpt == kQPT)
     nnd_finalize_cols_kernel<kTT, kQPT><<<grid_for(cp.count, di.sms), 256, 0, st>>>(cp);
   else
@@ -821,8 +938,8 @@ int twopass_impl(const float* q, int nq, const float* t, int nt, int b, int ndir
 
   PrepParams pp{};
   pp.nclouds = 2;
-  pp.c[0] = PrepCloud{q, soaq, nq, tiles_of(nq), (long long)b * tiles_of(nq) * kTT};
-  pp.c[1] = PrepCloud{t, soat, nt, tiles_of(nt), (long long)b * tiles_of(nt) * kTT};
+  pp.c[0] = PrepCloud{q, soaq, nq, tiles_of(nq), (long long)b * tiles_of(nq) * kTT, nq};
+  pp.c[1] = PrepCloud{t, soat, nt, tiles_of(nt), (long long)b * tiles_of(nt) * kTT, nt};
   pp.fill64[0] = keys;
   pp.count64[0] = (long long)b * nq;
   pp.fill64[1] = keys2;
@@ -935,7 +1052,7 @@ size_t nnd_workspace_bytes(int b, int n, int m) {
 
 size_t nnd_rows_workspace_bytes(int b, int n, int m) {
   if (b <= 0 || n <= 0 || m <= 0) return 256;
-  return soa_bytes(b, n) + soa_bytes(b, m) + key_bytes(b, n) + filter_bytes(b, m);
+  return rows_need(b, n, m);
 }
 
 size_t nnd_colkeys_count(int b, int m) {

@@ -42,6 +42,10 @@ struct FinColParams {
   int n, m, ttiles;
   long long count;  // b * m
   float one;
+  // cols / dist / idx may be a row range of a larger [b][col_stride] array starting at col_offset (role-swapped row
+  // ranges: the "columns" are rows [row_lo, row_hi) of xyz1); col_stride == m, col_offset == 0 otherwise.
+  long long col_stride;
+  int col_offset;
 };
 
 #ifdef NND_SYM_COUNT  // dev instrumentation (tools/slow_path_rate.py): slow-path entries / 4-target warp steps
@@ -326,7 +330,8 @@ __global__ void __launch_bounds__(256) nnd_finalize_cols_kernel(FinColParams p) 
     const unsigned long long key = p.ckeys[batch * p.ttiles * TT + k];
     const float bq = __uint_as_float((unsigned)(key >> 32));
     const long long j0 = (long long)(unsigned)(key & 0xffffffffull) * QPT;
-    const float* t = p.cols + g * 3;
+    const long long go = batch * p.col_stride + p.col_offset + k;  // position in cols / dist / idx
+    const float* t = p.cols + go * 3;
     const uint64_t TX = pk2(t[0], t[0]), TY = pk2(t[1], t[1]), TZ = pk2(t[2], t[2]);
     const float* rows = p.rows + batch * p.n * 3;
     int found = 0;
@@ -349,7 +354,7 @@ __global__ void __launch_bounds__(256) nnd_finalize_cols_kernel(FinColParams p) 
     float first, unused;
     upk2(sqdist2(TX, TY, TZ, pk2(-rows[0], -rows[0]), pk2(-rows[1], -rows[1]), pk2(-rows[2], -rows[2]), one), first, unused);
     const bool nan0 = first != first;
-    p.dist[g] = nan0 ? first : bq;
-    p.idx[g] = nan0 ? 0 : (int32_t)j;
+    p.dist[go] = nan0 ? first : bq;
+    p.idx[go] = nan0 ? 0 : (int32_t)j;
   }
 }

@@ -163,7 +163,8 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_symc_kernel(const __gr
 template <int TT>
 __global__ void __launch_bounds__(256) nnd_seed_filter_kernel(const float* __restrict__ cols, const float* __restrict__ qsoa,
                                                               unsigned* __restrict__ cdist, int m, int ttiles,
-                                                              int qtiles, int tile_first, int ns, float onef) {
+                                                              int qtiles, int tile_first, int ns, float onef,
+                                                              long long col_stride) {
   __shared__ __align__(16) float rows[3 * TT];
   const int batch = blockIdx.y;
   const uint64_t one = pk2(onef, onef);
@@ -175,7 +176,7 @@ __global__ void __launch_bounds__(256) nnd_seed_filter_kernel(const float* __res
   for (int k = 0; k < 2; ++k) {
     col[k] = blockIdx.x * 512 + k * 256 + threadIdx.x;
     const int c = col[k] < m ? col[k] : m - 1;
-    const float* s = cols + ((long long)batch * m + c) * 3;
+    const float* s = cols + ((long long)batch * col_stride + c) * 3;  // cols may be a row range of a larger cloud
     const float x = -s[0], y = -s[1], z = -s[2];
     ncx[k] = pk2(x, x);
     ncy[k] = pk2(y, y);

@@ -85,6 +85,74 @@ def test_row_ranges_at_scale_equal_the_single_launch(cuda_lib, device, kind):
         assert torch.equal(got, w)
 
 
+@pytest.mark.parametrize("kind,b,n,m,cuts", [
+    ("crosscopy", 1, 5000, 4100, (0, 2048, 5000)),             # second range longer than M: normal orientation
+    ("lattice", 2, 3001, 2500, (0, 8, 1000, 1000, 3001)),      # empty range, one-group range
+    ("identical", 1, 4096, 9000, (0, 4088, 4096)),
+    ("duplicates", 3, 700, 1300, (0, 696, 700)),
+    ("clustered", 1, 20000, 12000, (0, 4000, 4008, 11000, 20000)),
+    ("uniform", 2, 9000, 30000, (0, 3000, 9000)),              # every range shorter than M: role-swapped
+])
+def test_row_ranges_through_the_panel_scans(cuda_lib, device, kind, b, n, m, cuts):
+    """Same as above with every scan forced through the panel kernel: ranges shorter than M run role-swapped (xyz2 in
+    the registers, the range streamed; its partial results come back as column keys), the others in the normal
+    orientation.  Merged result == oracle, bit for bit."""
+    import oracle
+    from _util import assert_forward_exact
+    from pointcloudregistration_b200 import functional as F
+    from pointcloudregistration_b200 import synthetic
+
+    x1, x2 = synthetic.make_pair(kind, b, n, m, 74)
+    a, c = x1.to(device), x2.to(device)
+    d1 = torch.full((b, n), -1.0, device=device)
+    i1 = torch.full((b, n), -1, dtype=torch.int32, device=device)
+    before = cuda_lib.nnd_set_panel_min_rows(1)
+    try:
+        merged = None
+        for lo, hi in zip(cuts[:-1], cuts[1:]):
+            dr, ir, keys = F.nnd_forward_rows_raw(a, c, lo, hi)
+            d1[:, lo:hi], i1[:, lo:hi] = dr, ir
+            merged = keys if merged is None else torch.minimum(merged, keys)
+        d2, i2 = F.nnd_finalize_cols_raw(a, c, merged)
+    finally:
+        cuda_lib.nnd_set_panel_min_rows(before)
+    want = oracle.forward(x1.numpy(), x2.numpy(), threads=8)
+    assert_forward_exact(tuple(t.cpu().numpy() for t in (d1, d2, i1, i2)), want)
+
+
+def test_swapped_row_range_with_nonfinite_points(cuda_lib, device):
+    """NaN-first rule across role-swapped ranges: the rule is applied once, after the merge, not per range."""
+    import numpy as np
+    import oracle
+    from pointcloudregistration_b200 import functional as F
+    from pointcloudregistration_b200 import synthetic
+
+    x1 = synthetic.uniform(1, 4000, 75).numpy()
+    x2 = synthetic.uniform(1, 9000, 76).numpy()
+    x1[0, 0, 1] = np.nan      # first row of xyz1: every column's first candidate is NaN
+    x1[0, 2500] = np.inf
+    x2[0, 0] = np.nan         # first column: every row's first candidate is NaN
+    x2[0, 77, 2] = np.nan
+    a, c = torch.from_numpy(x1).to(device), torch.from_numpy(x2).to(device)
+    d1 = torch.empty(1, 4000, device=device)
+    i1 = torch.empty(1, 4000, dtype=torch.int32, device=device)
+    before = cuda_lib.nnd_set_panel_min_rows(1)
+    try:
+        merged = None
+        for lo, hi in ((0, 1600), (1600, 4000)):
+            dr, ir, keys = F.nnd_forward_rows_raw(a, c, lo, hi)
+            d1[:, lo:hi], i1[:, lo:hi] = dr, ir
+            merged = keys if merged is None else torch.minimum(merged, keys)
+        d2, i2 = F.nnd_finalize_cols_raw(a, c, merged)
+    finally:
+        cuda_lib.nnd_set_panel_min_rows(before)
+    w1, w2, j1, j2 = oracle.forward(x1, x2)
+    assert np.array_equal(i1.cpu().numpy(), j1) and np.array_equal(i2.cpu().numpy(), j2)
+    for got, want in ((d1, w1), (d2, w2)):
+        g = got.cpu().numpy()
+        assert np.array_equal(np.isnan(g), np.isnan(want)) and g[~np.isnan(g)].tobytes() == want[~np.isnan(want)].tobytes()
+
+
 def test_row_range_must_be_whole_groups(cuda_lib, device):
     from pointcloudregistration_b200 import functional as F
 
