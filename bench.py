@@ -397,6 +397,17 @@ def run_b200_arm(args, w):
         # distance evaluations one launch on one GPU executes (small clouds take the two-pass kernel: every pair)
         scan_evals = (pairs / 2 if symmetric else pairs) / world
         achieved = scan_evals * FP32_OPS_PER_PAIR / (scan_ms_avg * 1e-3) / 1e12
+        if not symmetric:
+            scan_kernel_name = "nnd_scan_kernel"
+        else:
+            from pointcloudregistration_b200.sharded import shard_range
+            lo, hi = shard_range(n, world, 0, align=lib.nnd_row_group()) if world > 1 else (0, n)
+            kind = lib.nnd_rows_scan_kind(n, m, lo, hi)
+            scan_kernel_name = {1: "nnd_scan_sym_kernel",
+                                2: "nnd_scan_symc_kernel (one launch per panel of columns on rotating streams; the "
+                                   "phase seed + all panel launches is timed as one)",
+                                3: "nnd_scan_symc_kernel, roles swapped (row shard streamed as columns; phase timed "
+                                   "as one)"}.get(kind, "nnd_scan_sym_kernel")
         peak = fp32_peak / 1e12
         traffic = None
         tfile = ROOT / "profiles" / "scan_traffic.json"
@@ -413,7 +424,7 @@ def run_b200_arm(args, w):
                                       "columns once); NCCL broadcast of both clouds, int64 MIN all_reduce of the "
                                       "column keys, all_gather of dist1/idx1, SUM all_reduce of gradients"
                                       if world > 1 else "single GPU"},
-            "roofline": {"bound": "fp32", "kernel": "nnd_scan_sym_kernel" if symmetric else "nnd_scan_kernel",
+            "roofline": {"bound": "fp32", "kernel": scan_kernel_name,
                          "achieved": achieved, "peak": peak,
                          "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                          "peak_source": f"148 SM x 128 FP32 lanes x sm_max_mhz {sm_max_mhz:.0f} MHz, {peak_src}; FMA is "

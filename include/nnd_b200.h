@@ -118,6 +118,10 @@ int nnd_backward_cuda_f32(const float *xyz1, const float *xyz2,
  * DESIGN.md section 4.0).  Results are bit-identical.  Sets the threshold (rows > 0) and returns the previous value;
  * rows <= 0 only queries.  Default 400000, or the environment variable NND_B200_PANEL_MIN_ROWS. */
 long long nnd_set_panel_min_rows(long long rows);
+/* Which scan nnd_forward_rows_cuda_f32 runs for rows [row_lo, row_hi) of an [n]-point xyz1 against an [m]-point xyz2:
+ * 1 = persistent symmetric kernel, 2 = panel kernel, 3 = panel kernel with the roles of the clouds swapped (ranges
+ * shorter than m), 0 = nothing to do.  (nnd_forward_cuda_f32 = the full range when nnd_forward_is_symmetric(n, m).) */
+int nnd_rows_scan_kind(int n, int m, int row_lo, int row_hi);
 /* Column tiles (512 points) per panel launch: 0 = chosen from the row count (default), 1, 2 or 4 = forced.  Returns the
  * previous setting; other values only query.  Environment: NND_B200_PANEL_TILES. */
 int nnd_set_panel_tiles(int tiles);

@@ -1064,6 +1064,14 @@ int nnd_row_group(void) { return kRowAlign; }
 
 int nnd_forward_is_symmetric(int n, int m) { return use_symmetric(n, m) ? 1 : 0; }
 
+int nnd_rows_scan_kind(int n, int m, int row_lo, int row_hi) {
+  const int nrows = row_hi - row_lo;
+  if (n <= 0 || m <= 0 || nrows <= 0) return 0;
+  if (nrows < m && m >= panel_min_rows() && m >= 2 * kTT && nrows >= panel_swap_min_rows()) return 3;
+  if (nrows >= panel_min_rows() && use_symmetric(n, m)) return 2;
+  return 1;
+}
+
 size_t nnd_query_workspace_bytes(int b, int nq, int nt) {
   if (b <= 0 || nq <= 0 || nt <= 0) return 256;
   return soa_bytes(b, nq) + soa_bytes(b, nt) + key_bytes(b, nq);
