@@ -9,27 +9,28 @@
 // (d = fl(fl(fl(dx*dx)+fl(dy*dy))+fl(dz*dz)), strict <, lowest index on ties), NOT
 // the FMA-contracted result nvcc produces from nnd_cuda.cu:28-31.
 //
-// Forward design (B200):
-//   * nnd_prepare_kernel rewrites each [n,3] cloud once into structure-of-arrays
-//     tiles  x[TT] | y[TT] | z[TT]  (last tile padded by repeating the last point:
-//     a duplicate at a higher index can never win the lowest-index tie-break).
-//   * nnd_scan_kernel: persistent CTAs; the work is the linear list of (direction, batch,
-//     query block, target tile) units and every CTA owns an equal contiguous share of it
-//     (balanced to one tile).  Target tiles arrive in shared memory by 1-D TMA bulk copies
-//     (cp.async.bulk + mbarrier, multi-stage ring).  Each thread keeps QPT queries in
-//     registers, duplicated into both halves of a 64-bit register pair and negated, so
-//     one packed instruction evaluates two targets:
+// Forward design (B200), three paths with bit-identical results:
+//   * nnd_prepare_kernel rewrites each [n,3] cloud once into structure-of-arrays tiles  x[TT] | y[TT] | z[TT]
+//     (last tile padded by repeating the last point: a duplicate at a higher index can never win the tie-break).
+//   * clouds below 8192 points: nnd_scan_kernel (this file), one scan per direction.  Persistent CTAs over the
+//     linear list of (direction, batch, query block, target tile) units, every CTA an equal contiguous share
+//     (balanced to one tile); target tiles arrive by 1-D TMA bulk copies (cp.async.bulk + mbarrier ring).
+//   * from 8192 points: nnd_scan_sym_kernel (nnd_sym.cuh): every distance is evaluated ONCE and serves both
+//     directions (row minima in registers, column minima through a filtered, warp-aggregated slow path).
+//   * row ranges from 400 000 rows (or any range against a cloud that large): nnd_scan_symc_kernel (nnd_symc.cuh),
+//     the same algorithm with the column points in UNIFORM registers, fed from the constant bank, one launch per
+//     panel of columns on rotating streams.
+//   Common to all: each thread keeps QPT rows in registers, negated, so one packed instruction evaluates two pairs:
 //         FADD2 x3 (t - q), FMUL2 x3 (squares), FFMA2 x2 with a run-time 1.0
 //         (fma(a,1,b) == fl(a+b); ptxas would contract mul.rn.f32x2 + add.rn.f32x2 into
 //          one FFMA2 and change the rounding, the run-time 1.0 makes that impossible)
-//     = 8 packed instructions per 2 pairs, each product and sum separately rounded.
-//   * minimum with one 3-input FMNMX per 2 pairs; the index is recovered lazily: per chunk
-//     of C targets the thread keeps only the chunk minimum and, when it beats the running
-//     best (strict <, ascending order), remembers WHICH chunk.
-//   * partial results of different CTAs merge through atomicMin on a packed
-//     (dist_bits << 32 | chunk_base) key: d >= +0 so uint order == float order, and the
-//     earlier chunk wins exact ties.  nnd_finalize_kernel re-evaluates that single chunk per
-//     query (same instruction sequence => same bits) and takes the lowest k with d == dist.
+//     = 8 packed instructions per 2 pairs, each product and sum separately rounded; minimum with one 3-input FMNMX
+//     per 2 pairs; the index is recovered lazily: per chunk of C targets the thread keeps only the chunk minimum and,
+//     when it beats the running best (strict <, ascending order), remembers WHICH chunk.
+//   * partial results of different CTAs / launches merge through atomicMin on a packed (dist_bits << 32 | chunk_base)
+//     key: d >= +0 so uint order == float order, and the earlier chunk wins exact ties.  nnd_finalize_kernel
+//     re-evaluates that single chunk per query (same instruction sequence => same bits) and takes the lowest k with
+//     d == dist.
 //
 // Backward: nnd_grad_kernel, one thread per (term, batch, row); warp-aggregated
 // (match.any on the neighbour index) fp32 atomics into zero-initialised grads.
@@ -849,8 +850,9 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   yp.one = 1.0f;
   const int grid_full = di.sms * si.minb;
   const int grid = yp.total_units < grid_full ? (int)yp.total_units : grid_full;
-  const size_t smem = sizeof(SymStage<kTT>) * kStages + (NND_SYM_LAZY ? (size_t)si.threads * si.qpt * 8 : 0);
-  if (shape == kShapeLarge && NND_SYM_LAZY == kChunk && nrows >= panel_min_rows()) {
+  const size_t smem = sizeof(SymStage<kTT>) * kStages + (size_t)si.threads * si.qpt * 8;  // ring + row bookkeeping
+  const bool panels = shape == kShapeLarge && nrows >= panel_min_rows();
+  if (panels) {
     SymCParams cp{};
     cp.qsoa = soa1;
     cp.rkeys = rkeys;
@@ -883,7 +885,7 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
     default: rc = launch_sym<128, 2, 8>(yp, grid, smem, st); break;
   }
   if (rc) return rc;
-  if (!(shape == kShapeLarge && NND_SYM_LAZY == kChunk && nrows >= panel_min_rows())) ++g_launches;
+  if (!panels) ++g_launches;
   if (ev) cudaEventRecord(ev[2], st);
   debug_sync("scan_sym", st);
 
@@ -891,7 +893,7 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   fp.ndir = 1;
   fp.one = 1.0f;
   fp.d[0] = FinDir{rkeys, c1, soa2, dist1, idx1, n1, tiles_of(n2), row_lo, nrows, (long long)b * nrows};
-  nnd_finalize_kernel<kTT, (NND_SYM_LAZY ? NND_SYM_LAZY : kChunk)><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
+  nnd_finalize_kernel<kTT, kChunk><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
   ++g_launches;
   if (ev) cudaEventRecord(ev[3], st);
   debug_sync("finalize_rows", st);

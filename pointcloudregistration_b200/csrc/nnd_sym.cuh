@@ -52,12 +52,6 @@ struct FinColParams {
 __device__ unsigned long long g_sym_slow, g_sym_steps;
 #endif
 
-#ifndef NND_SYM_ONE_VREG
-#define NND_SYM_ONE_VREG 0
-#endif
-#ifndef NND_SYM_LAZY
-#define NND_SYM_LAZY 32  // targets per lazy-index group of the row direction kept in shared memory; 0 = registers, per chunk
-#endif
 
 template <int TT>
 struct __align__(128) SymStage {
@@ -117,14 +111,12 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
   constexpr unsigned FULL = 0xffffffffu;
   extern __shared__ __align__(128) unsigned char sym_smem[];
   SymStage<TT>* stages = reinterpret_cast<SymStage<TT>*>(sym_smem);
-#if NND_SYM_LAZY
-  // Row bookkeeping lives in shared memory and is touched once per LG targets: previous best and the base of the
-  // LG-target group that produced it, per (row slot, thread).  Keeps 2*QPT registers free for the packed stream.
-  constexpr int LG = NND_SYM_LAZY;
-  static_assert(TT % LG == 0 && LG % C == 0, "lazy group shape");
+  // Row bookkeeping lives in shared memory and is touched once per C-target chunk: previous best and the base of the
+  // chunk that produced it, per (row slot, thread).  Keeps 2*QPT registers free for the packed stream
+  // (272.4 -> 270.4 ms at 1M; the run-time 1.0 stays a kernel parameter = uniform register: as a vector register it
+  // costs +3 %, profiles/r01_ubench_step.txt).
   float* sprev = reinterpret_cast<float*>(sym_smem + STAGES * sizeof(SymStage<TT>)) + threadIdx.x;
   int* sbase = reinterpret_cast<int*>(sprev - threadIdx.x + QPT * THREADS) + threadIdx.x;
-#endif
   __shared__ __align__(8) uint64_t full[STAGES];
 
   const int tid = threadIdx.x;
@@ -156,17 +148,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
       if (pu < u_end) produce(s);
   }
 
-#if NND_SYM_ONE_VREG
-  // keep the run-time 1.0 in an ordinary register: as a uniform register it is re-loaded from the constant bank
-  // every step (the warp vote's divergence check borrows the same uniform register)
-  __shared__ float s_one;
-  if (tid == 0) s_one = p.one;
-  __syncthreads();
-  const float onef = *reinterpret_cast<volatile float*>(&s_one);
-  const uint64_t one = pk2(onef, onef);
-#else
   const uint64_t one = pk2(p.one, p.one);
-#endif
   const float INF = __int_as_float(0x7f800000);
   uint32_t cnt = 0;
 
@@ -181,12 +163,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
 
     // ---- rows -> registers: QPT consecutive rows per thread
     uint64_t nqx[QPT], nqy[QPT], nqz[QPT];
-#if NND_SYM_LAZY
     float cm[QPT];  // running row minima of this segment
-#else
-    float best[QPT];
-    int bchunk[QPT];
-#endif
     const unsigned group = (unsigned)(p.row_lo / QPT + qblock * THREADS + tid);  // global row group id
     const float* qbase = p.qsoa + (long long)batch * p.qtiles * (3 * TT);
 #pragma unroll
@@ -199,14 +176,9 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
       nqx[q] = pk2(x, x);
       nqy[q] = pk2(y, y);
       nqz[q] = pk2(z, z);
-#if NND_SYM_LAZY
       cm[q] = INF;
       sprev[q * THREADS] = INF;
       sbase[q * THREADS] = 0;
-#else
-      best[q] = INF;
-      bchunk[q] = 0;
-#endif
     }
     unsigned long long* ckeys = p.ckeys + (long long)batch * p.ttiles * TT;
     unsigned* cdist = p.cdist + (long long)batch * p.ttiles * TT;
@@ -229,11 +201,6 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
         const ulonglong2* cx = reinterpret_cast<const ulonglong2*>(sx + ch * C);
         const ulonglong2* cy = reinterpret_cast<const ulonglong2*>(sy + ch * C);
         const ulonglong2* cz = reinterpret_cast<const ulonglong2*>(sz + ch * C);
-#if !NND_SYM_LAZY
-        float cm[QPT];
-#pragma unroll
-        for (int q = 0; q < QPT; ++q) cm[q] = INF;
-#endif
 #pragma unroll
         for (int s4 = 0; s4 < C / 4; ++s4) {
           const ulonglong2 X = cx[s4], Y = cy[s4], Z = cz[s4];
@@ -271,25 +238,15 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
 #ifdef NND_SYM_COUNT
         if (lane == 0) atomicAdd(&g_sym_steps, (unsigned long long)(C / 4));
 #endif
-#if NND_SYM_LAZY
-        if ((ch + 1) % (LG / C) == 0 || ch == nchunks - 1) {  // end of a lazy group: did it improve a row?
-          const int gbase = tile * TT + (ch / (LG / C)) * LG;
-#pragma unroll
-          for (int q = 0; q < QPT; ++q) {
-            if (cm[q] < sprev[q * THREADS]) {  // strict <, groups ascend: the earliest group with the minimum stays
-              sprev[q * THREADS] = cm[q];
-              sbase[q * THREADS] = gbase;
-            }
-          }
-        }
-#else
+        // end of the chunk: did it improve a row?  (strict <, chunks ascend: the earliest chunk with the minimum stays)
         const int cbase = tile * TT + ch * C;
 #pragma unroll
         for (int q = 0; q < QPT; ++q) {
-          if (cm[q] < best[q]) bchunk[q] = cbase;
-          best[q] = fminf(best[q], cm[q]);
+          if (cm[q] < sprev[q * THREADS]) {
+            sprev[q * THREADS] = cm[q];
+            sbase[q * THREADS] = cbase;
+          }
         }
-#endif
       }
       __syncthreads();
       if (tid == 0 && pu < u_end) {
@@ -304,13 +261,8 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
     for (int q = 0; q < QPT; ++q) {
       const int j = p.row_lo + qblock * QB + tid * QPT + q;
       if (j < p.row_hi) {
-#if NND_SYM_LAZY
         const unsigned long long key =
             ((unsigned long long)__float_as_uint(cm[q]) << 32) | (unsigned long long)(unsigned)sbase[q * THREADS];
-#else
-        const unsigned long long key =
-            ((unsigned long long)__float_as_uint(best[q]) << 32) | (unsigned long long)(unsigned)bchunk[q];
-#endif
         atomicMin(rkeys + j, key);
       }
     }
