@@ -409,10 +409,12 @@ def run_b200_arm(args, w):
                                 3: "nnd_scan_symc_kernel, roles swapped (row shard streamed as columns; phase timed "
                                    "as one)"}.get(kind, "nnd_scan_sym_kernel")
         peak = fp32_peak / 1e12
-        traffic = None
+        traffic = traffic_note = None
         tfile = ROOT / "profiles" / "scan_traffic.json"
         if tfile.exists():
-            traffic = json.loads(tfile.read_text()).get(f"{w['n']}x{w['m']}x{w['b']}")
+            tj = json.loads(tfile.read_text())
+            traffic = tj.get(f"{w['n']}x{w['m']}x{w['b']}")
+            traffic_note = tj.get("_note")
         cs = clocks.summary()
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup,
@@ -426,7 +428,7 @@ def run_b200_arm(args, w):
                                       if world > 1 else "single GPU"},
             "roofline": {"bound": "fp32", "kernel": scan_kernel_name,
                          "achieved": achieved, "peak": peak,
-                         "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
+                         "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note,
                          "peak_source": f"148 SM x 128 FP32 lanes x sm_max_mhz {sm_max_mhz:.0f} MHz, {peak_src}; FMA is "
                                         "forbidden by bit-exactness so 1 op = 1 lane-slot (the FMA-flop peak is 2x)",
                          "frac_of_fma_flop_peak": achieved / (2 * peak),
