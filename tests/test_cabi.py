@@ -70,7 +70,8 @@ def test_forward_kernel_sass_is_bit_exact_form():
     except (FileNotFoundError, subprocess.CalledProcessError):
         pytest.skip("cuobjdump not available")
     kernels = re.split(r"Function : ", out.stdout)
-    scan = [k for k in kernels if "nnd_scan_kernel" in k.split("\n", 1)[0] or "nnd_scan_sym_kernel" in k.split("\n", 1)[0]]
+    scan = [k for k in kernels if any(name in k.split("\n", 1)[0]
+                                      for name in ("nnd_scan_kernel", "nnd_scan_sym_kernel", "nnd_scan_symc_kernel"))]
     assert len(scan) >= 2, "nnd_scan_kernel / nnd_scan_sym_kernel not found in the cubin"
     for k in scan:
         ops = re.findall(r"^\s+/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", k, flags=re.M)
@@ -80,3 +81,25 @@ def test_forward_kernel_sass_is_bit_exact_form():
         assert 3 * n["FFMA2"] == 2 * n["FMUL2"], f"FFMA2:FMUL2 must be 2:3 (adds only), got {n}"
         assert n["FMNMX3"] > 0
     assert "UBLKCP" in out.stdout, "1-D TMA bulk copy (UBLKCP) missing from the forward kernel"
+
+
+def test_panel_kernel_keeps_its_columns_in_uniform_registers():
+    """The point of nnd_scan_symc_kernel: column points are loaded from the constant bank into UNIFORM
+    registers (LDCU c[0x3][UR..]) and consumed as UR operands of the packed adds.  ptxas silently falls back to LDC
+    into vector registers when the address arithmetic leaves the uniform datapath (tools/uniform_probe.cu); that
+    costs ~7 % and no parity test would notice, so the cubin is checked."""
+    from pointcloudregistration_b200 import _cabi
+
+    try:
+        out = subprocess.run(["cuobjdump", "-sass", str(_cabi.LIB_PATH)], capture_output=True, text=True, check=True)
+    except (FileNotFoundError, subprocess.CalledProcessError):
+        pytest.skip("cuobjdump not available")
+    kernels = [k for k in re.split(r"Function : ", out.stdout) if "nnd_scan_symc_kernel" in k.split("\n", 1)[0]]
+    assert len(kernels) == 6, "expected 3 panel sizes x (full, ragged) instantiations"
+    for k in kernels:
+        name = k.split("\n", 1)[0]
+        assert len(re.findall(r"LDCU(?:\.64|\.128)? UR\d+, c\[0x3\]\[UR", k)) >= 40, f"{name}: panel not loaded by LDCU"
+        assert not re.search(r"LDC(?:\.64|\.128)? R\d+, c\[0x3\]", k), f"{name}: panel loaded into vector registers"
+        ur_adds = len(re.findall(r"FADD2 R\d+, -?R\d+(?:\.reuse)?\.F32, UR\d+\.F32x2", k))
+        all_adds = len(re.findall(r"FADD2 ", k))
+        assert ur_adds == all_adds > 0, f"{name}: {ur_adds} of {all_adds} FADD2 take the column pair from a uniform register"
