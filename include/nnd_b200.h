@@ -116,7 +116,7 @@ int nnd_backward_cuda_f32(const float *xyz1, const float *xyz2,
 /* Tuning knob.  The symmetric forward has two scan kernels: the persistent TMA-fed one and, for row ranges of at least
  * this many rows, the "panel" one that keeps the column points in uniform registers (one launch per panel of columns,
  * DESIGN.md section 4.0).  Results are bit-identical.  Sets the threshold (rows > 0) and returns the previous value;
- * rows <= 0 only queries.  Default 400000, or the environment variable NND_B200_PANEL_MIN_ROWS. */
+ * rows <= 0 only queries.  Default 200000, or the environment variable NND_B200_PANEL_MIN_ROWS. */
 long long nnd_set_panel_min_rows(long long rows);
 /* Which scan nnd_forward_rows_cuda_f32 runs for rows [row_lo, row_hi) of an [n]-point xyz1 against an [m]-point xyz2:
  * 1 = persistent symmetric kernel, 2 = panel kernel, 3 = panel kernel with the roles of the clouds swapped (ranges

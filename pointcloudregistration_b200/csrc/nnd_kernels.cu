@@ -17,7 +17,7 @@
 //     (balanced to one tile); target tiles arrive by 1-D TMA bulk copies (cp.async.bulk + mbarrier ring).
 //   * from 8192 points: nnd_scan_sym_kernel (nnd_sym.cuh): every distance is evaluated ONCE and serves both
 //     directions (row minima in registers, column minima through a filtered, warp-aggregated slow path).
-//   * row ranges from 400 000 rows (or any range against a cloud that large): nnd_scan_symc_kernel (nnd_symc.cuh),
+//   * row ranges from 200 000 rows (or any range against a cloud that large): nnd_scan_symc_kernel (nnd_symc.cuh),
 //     the same algorithm with the column points in UNIFORM registers, fed from the constant bank, one launch per
 //     panel of columns on rotating streams.
 //   Common to all: each thread keeps QPT rows in registers, negated, so one packed instruction evaluates two pairs:
@@ -612,7 +612,7 @@ int g_panel_tiles = -1;  // 0 = choose from the row count; 1, 2, 4 = forced (tes
 long long panel_min_rows() {
   if (g_panel_min_rows < 0) {
     const char* e = getenv("NND_B200_PANEL_MIN_ROWS");
-    g_panel_min_rows = e ? atoll(e) : 400000;
+    g_panel_min_rows = e ? atoll(e) : 200000;
     if (g_panel_min_rows < 1) g_panel_min_rows = 1;
   }
   return g_panel_min_rows;

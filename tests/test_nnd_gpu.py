@@ -286,7 +286,7 @@ def test_aten_shim_writes_in_place(cuda_lib, device):
 # ---------------------------------------------------------------- the panel scan (columns in uniform registers)
 @pytest.fixture
 def panels_forced(cuda_lib):
-    """Push every symmetric scan through nnd_scan_symc_kernel (normally only row ranges >= 400 000 rows)."""
+    """Push every symmetric scan through nnd_scan_symc_kernel (normally only row ranges >= 200 000 rows)."""
     before = cuda_lib.nnd_set_panel_min_rows(1)
     yield
     cuda_lib.nnd_set_panel_min_rows(before)
