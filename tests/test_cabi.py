@@ -103,3 +103,23 @@ def test_panel_kernel_keeps_its_columns_in_uniform_registers():
         ur_adds = len(re.findall(r"FADD2 R\d+, -?R\d+(?:\.reuse)?\.F32, UR\d+\.F32x2", k))
         all_adds = len(re.findall(r"FADD2 ", k))
         assert ur_adds == all_adds > 0, f"{name}: {ur_adds} of {all_adds} FADD2 take the column pair from a uniform register"
+
+
+def test_scan_kind_selection_needs_no_gpu(cuda_lib):
+    """Which scan a row range takes (include/nnd_b200.h: nnd_rows_scan_kind): 1 persistent, 2 panel, 3 panel with
+    the roles of the clouds swapped."""
+    k = cuda_lib.nnd_rows_scan_kind
+    assert cuda_lib.nnd_set_panel_min_rows(0) == 200000            # query only
+    assert k(1_000_000, 1_000_000, 0, 1_000_000) == 2              # C4, one GPU
+    assert k(1_000_000, 1_000_000, 125_000, 250_000) == 3          # C4, one of 8 ranks: shorter than xyz2 -> swapped
+    assert k(262_144, 262_144, 0, 262_144) == 2                    # C5
+    assert k(100_000, 100_000, 0, 100_000) == 1                    # C3
+    assert k(100_000, 1_000_000, 0, 100_000) == 3                  # N < M on one GPU
+    assert k(1_000_000, 100_000, 0, 1_000_000) == 2                # N > M: rows in registers as usual
+    assert k(16_384, 16_384, 0, 0) == 0
+    before = cuda_lib.nnd_set_panel_min_rows(1)
+    try:
+        assert k(9000, 8200, 0, 9000) == 2 and k(9000, 30000, 0, 3000) == 3
+    finally:
+        cuda_lib.nnd_set_panel_min_rows(before)
+    assert cuda_lib.nnd_set_panel_tiles(3) == 0 and cuda_lib.nnd_set_panel_tiles(-1) == 0   # invalid values only query
