@@ -583,6 +583,8 @@ int launch_sym(const SymParams& yp, int grid, size_t smem, cudaStream_t st) {
 struct PanelCtx {
   cudaStream_t s[kPanelMaxBufs] = {};
   cudaEvent_t fork = nullptr, join[kPanelMaxBufs] = {};
+  cudaEvent_t done = nullptr;  // end of the last panel scan that was enqueued outside stream capture
+  bool have_done = false;
   bool ready = false;
 };
 std::mutex g_panel_mu;  // the constant window is per device: panel scans of one process are enqueued one at a time
@@ -599,6 +601,7 @@ int panel_ctx(PanelCtx** out) {
       if ((e = cudaEventCreateWithFlags(&c.join[i], cudaEventDisableTiming)) != cudaSuccess) return (int)e;
     }
     if ((e = cudaEventCreateWithFlags(&c.fork, cudaEventDisableTiming)) != cudaSuccess) return (int)e;
+    if ((e = cudaEventCreateWithFlags(&c.done, cudaEventDisableTiming)) != cudaSuccess) return (int)e;
     c.ready = true;
   }
   *out = &c;
@@ -656,9 +659,19 @@ int scan_panels(const SymCParams& yp, const float* soa2, int b, int qblocks, int
   int rc = panel_ctx(&c);
   if (rc) return rc;
   cudaError_t e;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if ((e = cudaStreamIsCapturing(st, &cap)) != cudaSuccess) return (int)e;
+  const bool capturing = cap != cudaStreamCaptureStatusNone;
   if ((e = cudaEventRecord(c->fork, st)) != cudaSuccess) return (int)e;
   for (int i = 0; i < kPanelMaxBufs; ++i)
     if ((e = cudaStreamWaitEvent(c->s[i], c->fork, 0)) != cudaSuccess) return (int)e;
+  // Scans enqueued from DIFFERENT caller streams share the constant window.  Buffer i is only ever written and read on
+  // internal stream i, which orders scans with the same panel size; scans with different panel sizes cut the window
+  // differently, so every internal stream also waits for the whole previous scan.  (Not expressible while capturing:
+  // a captured scan is ordered by its own stream only, and graph replays must not overlap other panel scans.)
+  if (!capturing && c->have_done)
+    for (int i = 0; i < kPanelMaxBufs; ++i)
+      if ((e = cudaStreamWaitEvent(c->s[i], c->done, 0)) != cudaSuccess) return (int)e;
   // launches in flight x CTAs per launch should cover the 2 * sms resident CTAs about twice
   if (g_panel_tiles < 0) g_panel_tiles = getenv("NND_B200_PANEL_TILES") ? atoi(getenv("NND_B200_PANEL_TILES")) : 0;
   int pt = qblocks * 2 >= 3 * sms ? 4 : qblocks * 4 >= 3 * sms ? 2 : 1;
@@ -670,6 +683,10 @@ int scan_panels(const SymCParams& yp, const float* soa2, int b, int qblocks, int
   for (int i = 0; i < kPanelMaxBufs; ++i) {
     if ((e = cudaEventRecord(c->join[i], c->s[i])) != cudaSuccess) return (int)e;
     if ((e = cudaStreamWaitEvent(st, c->join[i], 0)) != cudaSuccess) return (int)e;
+  }
+  if (!capturing) {
+    if ((e = cudaEventRecord(c->done, st)) != cudaSuccess) return (int)e;
+    c->have_done = true;
   }
   return check_last(cudaGetLastError());
 }

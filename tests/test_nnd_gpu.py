@@ -350,6 +350,37 @@ def test_panel_scan_under_graph_capture_and_side_stream(panels_forced, cuda_lib,
     assert_forward_exact(tuple(t.cpu().numpy() for t in cap), want2, what="graph replay: ")
 
 
+def test_panel_scans_from_two_streams_with_different_panel_sizes(panels_forced, cuda_lib, device):
+    """Panel scans share one constant window per device.  Two caller streams that alternate scans with different
+    panel sizes (the window is cut 2 x 4 tiles for one, 8 x 1 tile for the other) and never synchronise with each
+    other must still get the single-stream results."""
+    xa1, xa2 = synthetic.make_pair("uniform", 1, 30000, 24000, 46)
+    xb1, xb2 = synthetic.make_pair("clustered", 1, 16384, 20000, 47)
+    a1, a2, b1, b2 = (t.to(device) for t in (xa1, xa2, xb1, xb2))
+    try:
+        cuda_lib.nnd_set_panel_tiles(4)
+        want_a = tuple(t.cpu() for t in F.nnd_forward_raw(a1, a2))
+        cuda_lib.nnd_set_panel_tiles(1)
+        want_b = tuple(t.cpu() for t in F.nnd_forward_raw(b1, b2))
+        torch.cuda.synchronize()
+        sa, sb = torch.cuda.Stream(device=device), torch.cuda.Stream(device=device)
+        outs_a, outs_b = [], []
+        for _ in range(6):
+            cuda_lib.nnd_set_panel_tiles(4)
+            with torch.cuda.stream(sa):
+                outs_a.append(F.nnd_forward_raw(a1, a2))
+            cuda_lib.nnd_set_panel_tiles(1)
+            with torch.cuda.stream(sb):
+                outs_b.append(F.nnd_forward_raw(b1, b2))
+        torch.cuda.synchronize()
+    finally:
+        cuda_lib.nnd_set_panel_tiles(0)
+    for outs, want in ((outs_a, want_a), (outs_b, want_b)):
+        for out in outs:
+            for got, w in zip(out, want):
+                assert torch.equal(got.cpu(), w)
+
+
 def test_non_contiguous_inputs_and_side_stream(cuda_lib, device):
     import torch_nndistance as NND
 
