@@ -11,9 +11,10 @@ pair of synthetic clouds.  Pairs per step = 2*B*N*M (both directions).  Prints O
   value      Gpairs/s, whole job, inputs resident in HBM when the timed region starts
   e2e        the same metric through the public API (torch_nndistance.nnd + autograd) with HOST
              (pinned) inputs: H2D of both clouds, D2H of both gradients + the loss, every step
-  roofline   the dominant kernel (nnd_scan_kernel): 8 separately-rounded FP32 ops per pair (3 sub,
-             3 mul, 2 add -- FMA is forbidden by bit-exactness) / its CUDA-event duration measured
-             inside the timed steps, against the FP32 issue peak 148 SM x 128 lanes x sm_max_mhz
+  roofline   the dominant kernel (the scan: nnd_scan_symc_kernel at C4; roofline.kernel names it): 8
+             separately-rounded FP32 ops per evaluated distance (3 sub, 3 mul, 2 add -- FMA is forbidden
+             by bit-exactness) / the scan's CUDA-event duration measured inside the timed steps, against
+             the FP32 issue peak 148 SM x 128 lanes x sm_max_mhz
   cpu_baseline  the reference's own my_lib.cpp (oracle/_ref, unmodified) on all host cores, on a
              bounded query sample of the same workload, same run (N=1, rank 0 only)
 
@@ -48,6 +49,28 @@ WORKLOADS = {  # BASELINE.json configs
     "c4": dict(b=1, n=1_000_000, m=1_000_000, config=4, kind="uniform", desc="C4 large-cloud chamfer N=M=1M"),
     "c5": dict(b=1, n=262_144, m=262_144, config=5, kind="lattice", desc="C5 tie stress N=M=262144"),
 }
+
+
+_RESULT_FD = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout, but libraries write there too (NCCL prints its version line to stdout
+    when it initialises).  From here on everything written to fd 1 lands on stderr; emit() owns the real stdout."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
 
 
 def load_peaks():
@@ -169,7 +192,7 @@ def run_reference_arm(args, w):
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------------- reference GPU kernel
@@ -190,7 +213,7 @@ def run_reference_cuda_arm(args, w):
         return
     so = ROOT / "oracle" / "_ref" / "nnd_ref_cuda.so"
     if not so.exists():
-        print(json.dumps({"impl": "reference_cuda", "unavailable": "oracle/_ref/nnd_ref_cuda.so not built"}), flush=True)
+        emit({"impl": "reference_cuda", "unavailable": "oracle/_ref/nnd_ref_cuda.so not built"})
         return
     spec = importlib.util.spec_from_file_location("nnd_ref_cuda", str(so))
     mod = importlib.util.module_from_spec(spec)
@@ -231,7 +254,7 @@ def run_reference_cuda_arm(args, w):
             "data": "synthetic", "config": {"workload": w["desc"], "cloud": w["kind"], "b": b, "n": n, "m": m},
             "fraction_equal_to_b200_path": same,
             "note": "reference nnd_cuda.cu unmodified, nvcc defaults (FMA-contracted), sm_100a recompile"}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------------- GPU arm
@@ -285,10 +308,10 @@ def run_b200_arm(args, w):
             launches[0] += lib.nnd_last_launch_count()
         else:
             # rank 0's clouds are broadcast (NCCL over NVLink), rows sharded, results gathered / all-reduced
+            before = sharded.CudaCompute.launches  # this rank's kernels (prepare, seed, panel scans, finalizes, grad terms)
             d1, d2, i1, i2, info = sharded.sharded_forward(x1, x2, src=0, gather=True)
-            launches[0] += 4  # prepare, symmetric scan, row finalize, column finalize
             g1, g2 = sharded.sharded_backward(x1, x2, gd1, gd2, i1, i2, info, gathered=True)
-            launches[0] += 2
+            launches[0] += sharded.CudaCompute.launches - before
         return d1, d2, g1, g2
 
     for _ in range(warmup):
@@ -320,6 +343,10 @@ def run_b200_arm(args, w):
     total_ms, scan_ms_total = float(total_ms.item()), float(scan_ms.item())
     value = pairs * steps / (total_ms * 1e-3) / 1e9
     gpu_launches = launches[0]
+    if world > 1:  # whole job: every rank's kernels
+        lt = torch.tensor([launches[0]], dtype=torch.int64, device=dev)
+        dist.all_reduce(lt, op=dist.ReduceOp.SUM)
+        gpu_launches = int(lt.item())
 
     # backward alone (device events), for the secondary HBM roofline
     bwd_ms = None
@@ -452,7 +479,7 @@ def run_b200_arm(args, w):
                                     "ms": bwd_ms, "bytes": bytes_bwd, "note": "2 memsets + 1 kernel, timed together"}
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -470,6 +497,7 @@ def main():
     ap.add_argument("--cpu-cores", type=int, default=0, help="cap the host cores the CPU arm uses (0 = all)")
     ap.add_argument("--cpu-seconds-per-step", type=float, default=3.0, help="--impl reference: CPU work per step")
     args = ap.parse_args()
+    claim_stdout()
     w = dict(WORKLOADS[args.workload])
     cpu_arm.max_cores = args.cpu_cores or None
     if args.kind:

@@ -57,6 +57,14 @@ class ShardInfo:
 class CudaCompute:
     """Per-rank engine on the C ABI (include/nnd_b200.h).  No fallback."""
 
+    launches = 0  # kernels launched through this engine so far (bench.py's gpu_launches at N > 1)
+
+    @classmethod
+    def _count(cls) -> None:
+        from . import _cabi
+
+        cls.launches += int(_cabi.load().nnd_last_launch_count())
+
     @staticmethod
     def row_group() -> int:
         from .functional import row_group
@@ -68,13 +76,17 @@ class CudaCompute:
         """(dist1 [B,hi-lo], idx1 [B,hi-lo], colkeys int64) for rows [lo, hi) of xyz1 against all of xyz2."""
         from .functional import nnd_forward_rows_raw
 
-        return nnd_forward_rows_raw(xyz1, xyz2, lo, hi)
+        out = nnd_forward_rows_raw(xyz1, xyz2, lo, hi)
+        CudaCompute._count()
+        return out
 
     @staticmethod
     def finalize_cols(xyz1: torch.Tensor, xyz2: torch.Tensor, colkeys: torch.Tensor):
         from .functional import nnd_finalize_cols_raw
 
-        return nnd_finalize_cols_raw(xyz1, xyz2, colkeys)
+        out = nnd_finalize_cols_raw(xyz1, xyz2, colkeys)
+        CudaCompute._count()
+        return out
 
     @staticmethod
     def backward_term(q, t, gd, idx, grad_q, grad_t) -> None:
@@ -91,6 +103,7 @@ class CudaCompute:
             rc = lib.nnd_backward_term_cuda_f32(q.data_ptr(), t.data_ptr(), gd.data_ptr(), idx.data_ptr(), b, nq, nt,
                                                 grad_q.data_ptr(), grad_t.data_ptr(), _stream_ptr(q.device))
         _cabi.check(rc, "nnd_backward_term_cuda_f32")
+        CudaCompute._count()
 
 
 def _world(group):
