@@ -23,6 +23,11 @@
  *     my_lib.cpp:3-25 (lowest index on ties, no FMA contraction); gradients
  *     within 1e-5 relative of my_lib.cpp:91-130 (atomic summation order).
  *   - there is NO CPU fallback in this library.
+ *   - threads and streams: every call only enqueues work on `stream` and returns; calls may come from any host
+ *     thread.  Forwards over >= 200 000 rows (the panel scan) fork into library-owned streams and join back into
+ *     `stream` before returning, and share one constant-memory window per device: such forwards are serialised on
+ *     the device even when they come from different streams.  A panel scan captured into a CUDA graph is ordered
+ *     only by the stream that replays the graph; do not replay it concurrently with other large forwards.
  */
 #ifndef NND_B200_H
 #define NND_B200_H
