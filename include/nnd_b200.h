@@ -118,6 +118,23 @@ int nnd_backward_cuda_f32(const float *xyz1, const float *xyz2,
                           int b, int n, int m,
                           float *gradxyz1, float *gradxyz2, void *stream);
 
+/* Deterministic backward (opt-in; the reference has no such mode on the GPU -- its atomicAdd order is arbitrary,
+ * nnd_cuda.cu:175-180).  Same arguments and the same OVERWRITE semantics as nnd_backward_cuda_f32, but the gradients are
+ * BIT-IDENTICAL to the reference CPU path my_lib.cpp:91-130 (its sequential accumulation order is reproduced: sort of
+ * (neighbour row, own row) keys + one in-order pass per gradient row; no atomics, run-to-run deterministic).
+ * `workspace` = nnd_backward_exact_workspace_bytes(b, n, m) of 256-byte aligned device memory (0 = b*n or b*m
+ * exceeds 2^31 - 1, which this entry point rejects with NND_EINVAL).  Slower than the atomic kernel (measured at
+ * N = M = 1M: 0.41 ms against 0.06 ms on a uniform cloud, 9.1 ms against 0.14 ms on a clustered one, where thousands of
+ * rows share a neighbour and each such list is summed in order by one thread; profiles/r01_bwd_exact.txt) -- still
+ * 0.2 % / 3.6 % of the forward. */
+size_t nnd_backward_exact_workspace_bytes(int b, int n, int m);
+int nnd_backward_exact_cuda_f32(const float *xyz1, const float *xyz2,
+                                const float *graddist1, const float *graddist2,
+                                const int32_t *idx1, const int32_t *idx2,
+                                int b, int n, int m,
+                                float *gradxyz1, float *gradxyz2,
+                                void *workspace, size_t workspace_bytes, void *stream);
+
 /* Tuning knob.  The symmetric forward has two scan kernels: the persistent TMA-fed one and, for row ranges of at least
  * this many rows, the "panel" one that keeps the column points in uniform registers (one launch per panel of columns,
  * DESIGN.md section 4.0).  Results are bit-identical.  Sets the threshold (rows > 0) and returns the previous value;

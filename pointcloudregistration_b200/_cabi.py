@@ -39,6 +39,9 @@ SIGNATURES = {
                                        c_int, c_void_p, c_void_p, c_void_p]),
     "nnd_backward_term_cuda_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p,
                                             c_void_p, c_void_p]),
+    "nnd_backward_exact_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "nnd_backward_exact_cuda_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                             c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "nnd_last_launch_count": (c_int, []),
     "nnd_set_panel_min_rows": (c_longlong, [c_longlong]),
     "nnd_set_panel_tiles": (c_int, [c_int]),

@@ -34,6 +34,7 @@
 //
 // Backward: nnd_grad_kernel, one thread per (term, batch, row); warp-aggregated
 // (match.any on the neighbour index) fp32 atomics into zero-initialised grads.
+// Deterministic backward (opt-in): nnd_grad_exact_kernel (nnd_grad_exact.cuh), bit-identical to my_lib.cpp:91-130.
 
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -41,6 +42,8 @@
 #include <stdlib.h>
 
 #include <mutex>
+
+#include <cub/device/device_radix_sort.cuh>  // the deterministic backward sorts (neighbour row, own row) keys
 
 #include "nnd_b200.h"
 
@@ -438,6 +441,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
 // backward
 // ----------------------------------------------------------------------------------
 #include "nnd_grad.cuh"
+#include "nnd_grad_exact.cuh"
 
 // ----------------------------------------------------------------------------------
 // host side
@@ -1276,6 +1280,75 @@ int nnd_backward_cuda_f32(const float* xyz1, const float* xyz2, const float* gra
   gp.t[0] = GradTerm{xyz1, xyz2, graddist1, idx1, gradxyz1, gradxyz2, n, m, (long long)b * n};
   gp.t[1] = GradTerm{xyz2, xyz1, graddist2, idx2, gradxyz2, gradxyz1, m, n, (long long)b * m};
   return launch_grad(gp, st);
+}
+
+size_t nnd_backward_exact_workspace_bytes(int b, int n, int m) {
+  if (b <= 0 || n <= 0 || m <= 0) return 256;
+  const long long c1 = (long long)b * n, c2 = (long long)b * m;
+  if (c1 > 0x7fffffffLL || c2 > 0x7fffffffLL) return 0;  // rows are 32-bit halves of the sort keys
+  const size_t t1 = exact_sort_temp_bytes(c1), t2 = exact_sort_temp_bytes(c2);
+  return 2 * key_bytes(b, n) + 2 * key_bytes(b, m) + align_up(t1 > t2 ? t1 : t2, 256) + 256;
+}
+
+int nnd_backward_exact_cuda_f32(const float* xyz1, const float* xyz2, const float* graddist1, const float* graddist2,
+                                const int32_t* idx1, const int32_t* idx2, int b, int n, int m, float* gradxyz1,
+                                float* gradxyz2, void* workspace, size_t workspace_bytes, void* stream) {
+  g_launches = 0;
+  if (b < 0 || n < 0 || m < 0) return NND_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (b == 0) return 0;
+  if ((n > 0 && !gradxyz1) || (m > 0 && !gradxyz2)) return NND_EINVAL;
+  if (n == 0 || m == 0) {  // no pairs: both gradients are zero
+    cudaError_t e = cudaSuccess;
+    if (n > 0) e = cudaMemsetAsync(gradxyz1, 0, (size_t)b * n * 3 * sizeof(float), st);
+    if (m > 0 && e == cudaSuccess) e = cudaMemsetAsync(gradxyz2, 0, (size_t)b * m * 3 * sizeof(float), st);
+    return check_last(e);
+  }
+  if (!xyz1 || !xyz2 || !graddist1 || !graddist2 || !idx1 || !idx2 || !workspace) return NND_EINVAL;
+  const long long c1 = (long long)b * n, c2 = (long long)b * m;
+  if (c1 > 0x7fffffffLL || c2 > 0x7fffffffLL) return NND_EINVAL;
+  if (((uintptr_t)workspace & 255u) != 0) return NND_EWORKSPACE;
+  const size_t t1 = exact_sort_temp_bytes(c1), t2 = exact_sort_temp_bytes(c2);
+  const size_t temp_bytes = align_up(t1 > t2 ? t1 : t2, 256) + 256;
+  if (workspace_bytes < 2 * key_bytes(b, n) + 2 * key_bytes(b, m) + temp_bytes) return NND_EWORKSPACE;
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  char* w = (char*)workspace;
+  unsigned long long* k1_in = (unsigned long long*)w;   // from idx1: (cloud-2 row << 32 | cloud-1 row), c1 keys
+  w += key_bytes(b, n);
+  unsigned long long* k1_out = (unsigned long long*)w;
+  w += key_bytes(b, n);
+  unsigned long long* k2_in = (unsigned long long*)w;   // from idx2: (cloud-1 row << 32 | cloud-2 row), c2 keys
+  w += key_bytes(b, m);
+  unsigned long long* k2_out = (unsigned long long*)w;
+  w += key_bytes(b, m);
+  void* temp = (void*)w;
+
+  ExactKeyParams kp{};
+  kp.s[0] = ExactKeySide{idx1, k1_in, n, m, c1};
+  kp.s[1] = ExactKeySide{idx2, k2_in, m, n, c2};
+  const long long most = c1 > c2 ? c1 : c2;
+  nnd_exact_keys_kernel<<<grid_for(most, di.sms), 256, 0, st>>>(kp);
+  ++g_launches;
+  int end1 = 32 + bits_for((unsigned long long)c2), end2 = 32 + bits_for((unsigned long long)c1);
+  end1 = end1 > 64 ? 64 : end1;
+  end2 = end2 > 64 ? 64 : end2;
+  size_t tb = temp_bytes;
+  cudaError_t e = cub::DeviceRadixSort::SortKeys(temp, tb, (const unsigned long long*)k1_in, k1_out, (int)c1, 0, end1, st);
+  if (e != cudaSuccess) return (int)e;
+  tb = temp_bytes;
+  e = cub::DeviceRadixSort::SortKeys(temp, tb, (const unsigned long long*)k2_in, k2_out, (int)c2, 0, end2, st);
+  if (e != cudaSuccess) return (int)e;
+
+  ExactParams ep{};
+  // cloud 1: own term (term 1) first, then the term-2 contributions of the cloud-2 rows that chose it (keys from idx2)
+  ep.s[0] = ExactSide{xyz1, xyz2, graddist1, graddist2, idx1, k2_out, gradxyz1, n, m, c1, c2, 1};
+  // cloud 2: the term-1 contributions of the cloud-1 rows that chose it (keys from idx1) first, then its own term
+  ep.s[1] = ExactSide{xyz2, xyz1, graddist2, graddist1, idx2, k1_out, gradxyz2, m, n, c2, c1, 0};
+  nnd_grad_exact_kernel<<<grid_for(most, di.sms), 256, 0, st>>>(ep);
+  ++g_launches;
+  return check_last(cudaGetLastError());
 }
 
 }  // extern "C"

@@ -137,8 +137,26 @@ def nnd_query_raw(query: torch.Tensor, target: torch.Tensor):
     return dist, idx
 
 
-def nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2):
-    """gradxyz1[B,N,3], gradxyz2[B,M,3] (my_lib.cpp:64-133 semantics, both always produced)."""
+_exact_backward = None  # None: follow torch.are_deterministic_algorithms_enabled()
+
+
+def set_exact_backward(on) -> None:
+    """True: every backward takes the deterministic kernel (gradients bit-identical to my_lib.cpp:91-130, ~5x the
+    time of the atomic kernel, still ~0.1 % of a large forward).  False: always the atomic kernel (1e-5 contract).
+    None (default): deterministic exactly when torch.use_deterministic_algorithms(True) is in force."""
+    global _exact_backward
+    _exact_backward = on
+
+
+def exact_backward_enabled() -> bool:
+    if _exact_backward is None:
+        return bool(torch.are_deterministic_algorithms_enabled())
+    return bool(_exact_backward)
+
+
+def nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2, exact=None):
+    """gradxyz1[B,N,3], gradxyz2[B,M,3] (my_lib.cpp:64-133 semantics, both always produced).
+    exact=True: nnd_backward_exact_cuda_f32 (bit-identical to the reference CPU path); None: see set_exact_backward."""
     _check_clouds(xyz1, xyz2)
     lib = _cabi.load()
     xyz1 = xyz1.contiguous()
@@ -156,7 +174,20 @@ def nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2):
     idx2 = idx2.contiguous()
     gradxyz1 = torch.empty_like(xyz1)
     gradxyz2 = torch.empty_like(xyz2)
+    if exact is None:
+        exact = exact_backward_enabled()
     with torch.cuda.device(dev):
+        if exact:
+            nbytes = lib.nnd_backward_exact_workspace_bytes(b, n, m)
+            if nbytes == 0:
+                raise ValueError("deterministic backward supports at most 2^31 - 1 points per cloud tensor")
+            ws = _workspace(nbytes, dev)
+            rc = lib.nnd_backward_exact_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), graddist1.data_ptr(),
+                                                 graddist2.data_ptr(), idx1.data_ptr(), idx2.data_ptr(), b, n, m,
+                                                 gradxyz1.data_ptr(), gradxyz2.data_ptr(), ws.data_ptr(), ws.numel(),
+                                                 _stream_ptr(dev))
+            _cabi.check(rc, "nnd_backward_exact_cuda_f32")
+            return gradxyz1, gradxyz2
         rc = lib.nnd_backward_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), graddist1.data_ptr(), graddist2.data_ptr(),
                                        idx1.data_ptr(), idx2.data_ptr(), b, n, m, gradxyz1.data_ptr(),
                                        gradxyz2.data_ptr(), _stream_ptr(dev))

@@ -61,3 +61,26 @@ def test_product_never_imports_the_oracle():
     for f in files:
         src = f.read_text()
         assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f"{f} imports the oracle"
+
+
+def test_exact_backward_switch_follows_torch_deterministic_mode():
+    """functional.set_exact_backward: None follows torch.use_deterministic_algorithms, True/False override it."""
+    import torch
+
+    from pointcloudregistration_b200 import functional as F
+
+    before = torch.are_deterministic_algorithms_enabled()
+    try:
+        F.set_exact_backward(None)
+        torch.use_deterministic_algorithms(False)
+        assert not F.exact_backward_enabled()
+        torch.use_deterministic_algorithms(True)
+        assert F.exact_backward_enabled()
+        F.set_exact_backward(False)
+        assert not F.exact_backward_enabled()
+        torch.use_deterministic_algorithms(False)
+        F.set_exact_backward(True)
+        assert F.exact_backward_enabled()
+    finally:
+        F.set_exact_backward(None)
+        torch.use_deterministic_algorithms(before)

@@ -19,10 +19,20 @@ def gpu_forward(x1, x2, device):
     return tuple(t.cpu().numpy() for t in out)
 
 
-def gpu_backward(x1, x2, gd1, gd2, i1, i2, device):
+def gpu_backward(x1, x2, gd1, gd2, i1, i2, device, exact=False):
     t = [torch.as_tensor(np.asarray(a)).to(device) for a in (x1, x2, gd1, gd2, i1, i2)]
-    g1, g2 = F.nnd_backward_raw(*t)
+    g1, g2 = F.nnd_backward_raw(*t, exact=exact)
     return g1.cpu().numpy(), g2.cpu().numpy()
+
+
+def assert_grad_bits(got, want, what=""):
+    """The deterministic backward: every gradient bit equal to the reference CPU path's."""
+    for name, g, w in zip(("gradxyz1", "gradxyz2"), got, want):
+        g, w = np.ascontiguousarray(g), np.ascontiguousarray(w, dtype=np.float32)
+        assert g.shape == w.shape, f"{what}{name}: shape {g.shape} vs {w.shape}"
+        bad = np.flatnonzero(g.reshape(-1).view(np.int32) != w.reshape(-1).view(np.int32))
+        assert bad.size == 0, (f"{what}{name}: {bad.size} of {g.size} entries differ in bits; first at {int(bad[0])}: "
+                               f"got {g.reshape(-1)[bad[0]]!r} want {w.reshape(-1)[bad[0]]!r}")
 
 
 # ---------------------------------------------------------------- golden vectors (reference outputs)
@@ -33,6 +43,8 @@ def test_golden_vectors(name, cuda_lib, device):
     assert_forward_exact(got, (z["dist1"], z["dist2"], z["idx1"], z["idx2"]), what=name + ": ")
     g = gpu_backward(z["xyz1"], z["xyz2"], z["graddist1"], z["graddist2"], z["idx1"], z["idx2"], device)
     assert_grad_close(g, (z["grad1"], z["grad2"]), what=name + ": ")
+    g = gpu_backward(z["xyz1"], z["xyz2"], z["graddist1"], z["graddist2"], z["idx1"], z["idx2"], device, exact=True)
+    assert_grad_bits(g, (z["grad1"], z["grad2"]), what=name + " (deterministic backward): ")
 
 
 @pytest.mark.parametrize("name", DIGEST_CASES)
@@ -68,6 +80,60 @@ def test_data_kinds(kind, b, n, m, cuda_lib, device):
     gd1, gd2 = synthetic.grad_pair(b, n, m, 41)
     wg = oracle.backward(x1.numpy(), x2.numpy(), gd1.numpy(), gd2.numpy(), want[2], want[3])
     assert_grad_close(gpu_backward(x1, x2, gd1, gd2, got[2], got[3], device), wg, what=f"{kind}: ")
+    assert_grad_bits(gpu_backward(x1, x2, gd1, gd2, got[2], got[3], device, exact=True), wg, what=f"{kind} (exact): ")
+
+
+# ---------------------------------------------------------------- deterministic backward (bit-identical to my_lib.cpp:91-130)
+@pytest.mark.parametrize("kind,b,n,m", [
+    ("uniform", 1, 1, 1), ("uniform", 3, 7, 5), ("uniform", 2, 2049, 1000), ("clustered", 1, 20000, 1500),
+    ("identical", 1, 4096, 4096),      # every cloud-2 row is chosen by two rows: ordered pairs everywhere
+    ("duplicates", 4, 3000, 2000), ("lattice", 1, 30000, 30000), ("clustered", 1, 262144, 200000),
+])
+def test_deterministic_backward_is_bit_identical_to_the_reference_cpu_path(kind, b, n, m, cuda_lib, device):
+    x1, x2 = synthetic.make_pair(kind, b, n, m, 48)
+    d1, d2, i1, i2 = gpu_forward(x1, x2, device)
+    gd1, gd2 = synthetic.grad_pair(b, n, m, 48)
+    want = oracle.backward(x1.numpy(), x2.numpy(), gd1.numpy(), gd2.numpy(), i1, i2)
+    got = gpu_backward(x1, x2, gd1, gd2, i1, i2, device, exact=True)
+    assert_grad_bits(got, want, what=f"{kind} b{b} n{n} m{m}: ")
+    again = gpu_backward(x1, x2, gd1, gd2, i1, i2, device, exact=True)
+    assert got[0].tobytes() == again[0].tobytes() and got[1].tobytes() == again[1].tobytes()
+
+
+def test_deterministic_backward_one_neighbour_for_everybody_and_denormals(cuda_lib, device):
+    """All 50 000 rows of cloud 1 choose the same point (one 50 000-entry segment, summed in order by one thread), and
+    upstream gradients small enough that products and sums are denormal (the atomic path flushes those, this one
+    must not)."""
+    n, m = 50000, 40
+    x1 = torch.rand(1, n, 3, generator=torch.Generator().manual_seed(5)) * 0.01
+    x2 = torch.rand(1, m, 3, generator=torch.Generator().manual_seed(6)) + 5.0
+    x2[0, 17] = 0.005
+    d1, d2, i1, i2 = gpu_forward(x1, x2, device)
+    assert (i1 == 17).all()
+    for scale in (1.0, 1e-38):
+        gd1 = torch.rand(1, n, generator=torch.Generator().manual_seed(7)) * scale
+        gd2 = torch.rand(1, m, generator=torch.Generator().manual_seed(8)) * scale
+        want = oracle.backward(x1.numpy(), x2.numpy(), gd1.numpy(), gd2.numpy(), i1, i2)
+        assert_grad_bits(gpu_backward(x1, x2, gd1, gd2, i1, i2, device, exact=True), want, what=f"scale {scale}: ")
+
+
+def test_deterministic_backward_through_autograd(cuda_lib, device):
+    import torch_nndistance as NND
+    from pointcloudregistration_b200 import set_exact_backward
+
+    x1, x2 = synthetic.make_pair("clustered", 2, 5000, 4000, 49)
+    a = x1.to(device).requires_grad_(True)
+    c = x2.to(device).requires_grad_(True)
+    set_exact_backward(True)
+    try:
+        d1, d2, i1, i2 = NND.nnd_with_idx(a, c)
+        (d1.sum() * 0.25 + d2.sum() * 0.5).backward()
+    finally:
+        set_exact_backward(None)
+    gd1 = np.full((2, 5000), 0.25, np.float32)
+    gd2 = np.full((2, 4000), 0.5, np.float32)
+    want = oracle.backward(x1.numpy(), x2.numpy(), gd1, gd2, i1.cpu().numpy(), i2.cpu().numpy())
+    assert_grad_bits((a.grad.cpu().numpy(), c.grad.cpu().numpy()), want, what="autograd: ")
 
 
 def test_adversarial_ties_across_chunks_and_tiles(cuda_lib, device):
@@ -473,6 +539,7 @@ def test_config4_one_million(kind, cuda_lib, device):
     assert np.abs(tot).max() <= 1e-5 * mag
     wg = oracle.backward(x1.numpy(), x2.numpy(), gd1.numpy(), gd2.numpy(), got[2], got[3])
     assert_grad_close((g1, g2), wg)
+    assert_grad_bits(gpu_backward(x1, x2, gd1, gd2, got[2], got[3], device, exact=True), wg, what=f"1M {kind} (exact): ")
 
 
 def test_config3_ndp_loop_100k(cuda_lib, device):
