@@ -124,9 +124,9 @@ int nnd_backward_cuda_f32(const float *xyz1, const float *xyz2,
  * (neighbour row, own row) keys + one in-order pass per gradient row; no atomics, run-to-run deterministic).
  * `workspace` = nnd_backward_exact_workspace_bytes(b, n, m) of 256-byte aligned device memory (0 = b*n or b*m
  * exceeds 2^31 - 1, which this entry point rejects with NND_EINVAL).  Slower than the atomic kernel (measured at
- * N = M = 1M: 0.41 ms against 0.06 ms on a uniform cloud, 9.1 ms against 0.14 ms on a clustered one, where thousands of
- * rows share a neighbour and each such list is summed in order by one thread; profiles/r01_bwd_exact.txt) -- still
- * 0.2 % / 3.6 % of the forward. */
+ * N = M = 1M: 0.41 ms against 0.06 ms on a uniform cloud, 2.5 ms against 0.15 ms on a clustered one, where thousands of
+ * rows share a neighbour and each such list has to be summed in order; profiles/r01_bwd_exact.txt) -- still
+ * 0.2 % / 1 % of the forward. */
 size_t nnd_backward_exact_workspace_bytes(int b, int n, int m);
 int nnd_backward_exact_cuda_f32(const float *xyz1, const float *xyz2,
                                 const float *graddist1, const float *graddist2,
