@@ -83,20 +83,6 @@ __device__ __forceinline__ float fmin3(float a, float b, float c) {
   return r;
 }
 
-// min for operands that are both >= +0: |min(|a|,|b|)| with sign = sign(a)^sign(b) = +.  Same value as
-// min.f32 on such inputs, but a different opcode flavour, which keeps ptxas from merging two 2-input
-// FMNMX into one 3-input FMNMX3 (measured slower inside a saturated packed-FP32 stream).
-__device__ __forceinline__ float fmin_xs(float a, float b) {
-  float r;
-  asm("min.xorsign.abs.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
-  return r;
-}
-
-// 3-input minimum on the bit patterns as signed integers (for operands >= +0 this is the float minimum)
-__device__ __forceinline__ float imin3f(float a, float b, float c) {
-  return __int_as_float(min(min(__float_as_int(a), __float_as_int(b)), __float_as_int(c)));
-}
-
 // Two squared distances at once.  T* = {t[k], t[k+1]}, nq* = {-q, -q}, one = {1.0f, 1.0f}
 // passed at run time.  Every operation rounds separately (my_lib.cpp:12-15).
 __device__ __forceinline__ uint64_t sqdist2(uint64_t TX, uint64_t TY, uint64_t TZ, uint64_t nqx,
