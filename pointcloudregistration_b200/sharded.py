@@ -13,6 +13,10 @@ needed in full on every rank (12 MB per million points), so they are broadcast o
               all_gather(dist1/idx1 row shards)           [optional: gather=False keeps shards]
     backward: term 1 over the own xyz1 rows, term 2 over the own slice of xyz2 rows,
               all_reduce(SUM) of gradxyz1, gradxyz2       (scatter terms land anywhere in the other cloud)
+    backward, deterministic mode (functional.set_exact_backward / torch.use_deterministic_algorithms):
+              every rank already holds the full idx / graddist, so each runs the whole deterministic backward
+              (0.4 ms at 1M points) -- no collective, gradients bit-identical on every rank, for any G, and to
+              the reference CPU path
 
 Forward results are bit-identical for any G: row results are a pure per-row function, and a column
 key (dist_bits << 32 | row_group) is an order-independent integer minimum.  Gradients differ from
@@ -105,6 +109,21 @@ class CudaCompute:
         _cabi.check(rc, "nnd_backward_term_cuda_f32")
         CudaCompute._count()
 
+    @staticmethod
+    def exact_default() -> bool:
+        from .functional import exact_backward_enabled
+
+        return exact_backward_enabled()
+
+    @staticmethod
+    def backward_exact(xyz1, xyz2, graddist1, graddist2, idx1, idx2):
+        """Both full gradients, bit-identical to my_lib.cpp:91-130 (nnd_backward_exact_cuda_f32)."""
+        from .functional import nnd_backward_raw
+
+        out = nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2, exact=True)
+        CudaCompute._count()
+        return out
+
 
 def _world(group):
     if not dist.is_available() or not dist.is_initialized():
@@ -163,10 +182,25 @@ def sharded_forward(xyz1, xyz2, group=None, src=None, gather=True, compute=CudaC
 
 
 def sharded_backward(xyz1, xyz2, graddist1, graddist2, idx1, idx2, info: ShardInfo, group=None, gathered=True,
-                     compute=CudaCompute):
+                     compute=CudaCompute, exact=None):
     """Full-size gradxyz1, gradxyz2, identical on every rank (all_reduce SUM of per-rank partials).
-    graddist*/idx* are full-size when gathered=True, else this rank's shards."""
+    graddist*/idx* are full-size when gathered=True, else this rank's shards.
+    exact (None = the engine's default, i.e. functional.exact_backward_enabled()): the deterministic backward,
+    replicated on every rank from the full idx / graddist -- no collective, bit-identical gradients for any G."""
     lo1, hi1, lo2, hi2 = info.lo1, info.hi1, info.lo2, info.hi2
+    if exact is None:
+        exact = bool(getattr(compute, "exact_default", lambda: False)())
+    if exact:
+        if not gathered and info.world > 1:  # shards in: one all_gather per cloud (bits side by side, like the forward)
+            n, m, b = xyz1.size(1), xyz2.size(1), xyz1.size(0)
+            both1 = _gather_rows(torch.cat([graddist1.contiguous().view(torch.int32), idx1.contiguous()], dim=0), n,
+                                 info.world, group, compute.row_group())
+            both2 = _gather_rows(torch.cat([graddist2.contiguous().view(torch.int32), idx2.contiguous()], dim=0), m,
+                                 info.world, group, 1)
+            graddist1, idx1 = both1[:b].clone().view(torch.float32), both1[b:].clone()
+            graddist2, idx2 = both2[:b].clone().view(torch.float32), both2[b:].clone()
+        return compute.backward_exact(xyz1, xyz2, graddist1.contiguous(), graddist2.contiguous(), idx1.contiguous(),
+                                      idx2.contiguous())
     if gathered:
         graddist1, idx1 = graddist1[:, lo1:hi1], idx1[:, lo1:hi1]
         graddist2, idx2 = graddist2[:, lo2:hi2], idx2[:, lo2:hi2]
@@ -189,10 +223,10 @@ class ShardedNNDFunction(Function):
     """nnd with the query rows sharded over the ranks of `group`; inputs and outputs replicated."""
 
     @staticmethod
-    def forward(ctx, xyz1, xyz2, group, src, compute):
+    def forward(ctx, xyz1, xyz2, group, src, compute, exact=None):
         d1, d2, i1, i2, info = sharded_forward(xyz1, xyz2, group=group, src=src, gather=True, compute=compute)
         ctx.save_for_backward(xyz1, xyz2, i1, i2)
-        ctx.info, ctx.group, ctx.compute = info, group, compute
+        ctx.info, ctx.group, ctx.compute, ctx.exact = info, group, compute, exact
         ctx.mark_non_differentiable(i1, i2)
         return d1, d2, i1, i2
 
@@ -200,15 +234,16 @@ class ShardedNNDFunction(Function):
     def backward(ctx, gd1, gd2, _a, _b):
         xyz1, xyz2, i1, i2 = ctx.saved_tensors
         g1, g2 = sharded_backward(xyz1, xyz2, gd1.contiguous(), gd2.contiguous(), i1, i2, ctx.info, group=ctx.group,
-                                  gathered=True, compute=ctx.compute)
-        return g1, g2, None, None, None
+                                  gathered=True, compute=ctx.compute, exact=ctx.exact)
+        return g1, g2, None, None, None, None
 
 
-def nnd_sharded(xyz1, xyz2, group=None, src=None, compute=CudaCompute):
-    """dist1, dist2 = nnd_sharded(xyz1, xyz2): same contract as nnd(), computed by all ranks together."""
-    d1, d2, _, _ = ShardedNNDFunction.apply(xyz1, xyz2, group, src, compute)
+def nnd_sharded(xyz1, xyz2, group=None, src=None, compute=CudaCompute, exact=None):
+    """dist1, dist2 = nnd_sharded(xyz1, xyz2): same contract as nnd(), computed by all ranks together.
+    exact: deterministic backward (None = follow functional.set_exact_backward / torch's deterministic mode)."""
+    d1, d2, _, _ = ShardedNNDFunction.apply(xyz1, xyz2, group, src, compute, exact)
     return d1, d2
 
 
-def nnd_sharded_with_idx(xyz1, xyz2, group=None, src=None, compute=CudaCompute):
-    return ShardedNNDFunction.apply(xyz1, xyz2, group, src, compute)
+def nnd_sharded_with_idx(xyz1, xyz2, group=None, src=None, compute=CudaCompute, exact=None):
+    return ShardedNNDFunction.apply(xyz1, xyz2, group, src, compute, exact)

@@ -81,6 +81,15 @@ class OracleCompute:
             np.subtract.at(grad_t[b].numpy(), ix[b], tt)
 
 
+    @staticmethod
+    def backward_exact(xyz1, xyz2, gd1, gd2, idx1, idx2):
+        import oracle
+
+        g1, g2 = oracle.backward(xyz1.detach().numpy(), xyz2.detach().numpy(), gd1.numpy(), gd2.numpy(), idx1.numpy(),
+                                 idx2.numpy())
+        return torch.from_numpy(g1), torch.from_numpy(g2)
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -106,7 +115,17 @@ def _worker(rank, world, port, b, n, m, out):
         d1, d2, i1, i2 = sharded.nnd_sharded_with_idx(a, c, src=None, compute=OracleCompute)
         gd1, gd2 = synthetic.grad_pair(b, n, m, 60)
         ((d1 * gd1).sum() + (d2 * gd2).sum()).backward()
-        torch.save(dict(d1=d1.detach(), d2=d2.detach(), i1=i1, i2=i2, g1=a.grad, g2=c.grad), f"{out}/r{rank}.pt")
+        # deterministic mode: replicated full backward from the gathered idx / graddist, no collective
+        a2 = a.detach().clone().requires_grad_(True)
+        c2 = c.detach().clone().requires_grad_(True)
+        e1, e2, _, _ = sharded.nnd_sharded_with_idx(a2, c2, src=None, compute=OracleCompute, exact=True)
+        ((e1 * gd1).sum() + (e2 * gd2).sum()).backward()
+        # ... and from shards (gathered=False): graddist / idx are all-gathered first
+        f1, f2, j1s, j2s, info_s = sharded.sharded_forward(a.detach(), c.detach(), gather=False, compute=OracleCompute)
+        x_g1, x_g2 = sharded.sharded_backward(a.detach(), c.detach(), gd1[:, info_s.lo1:info_s.hi1], gd2[:, info_s.lo2:info_s.hi2],
+                                              j1s, j2s, info_s, gathered=False, compute=OracleCompute, exact=True)
+        torch.save(dict(d1=d1.detach(), d2=d2.detach(), i1=i1, i2=i2, g1=a.grad, g2=c.grad, e1=a2.grad, e2=c2.grad,
+                        x1=x_g1, x2=x_g2), f"{out}/r{rank}.pt")
         # shard-only mode + explicit broadcast from src
         y1, y2 = synthetic.make_pair("crosscopy", b, n, m, 60)
         if rank != 0:
@@ -133,6 +152,8 @@ def test_sharded_matches_unsharded(world, b, n, m, tmp_path):
         z = torch.load(f"{tmp_path}/r{r}.pt")
         assert_forward_exact(tuple(z[k].numpy() for k in ("d1", "d2", "i1", "i2")), want, what=f"rank {r}: ")
         assert_grad_close((z["g1"].numpy(), z["g2"].numpy()), wg, what=f"rank {r}: ")
+        for k1, k2 in (("e1", "e2"), ("x1", "x2")):  # deterministic mode: every bit, on every rank
+            assert z[k1].numpy().tobytes() == wg[0].tobytes() and z[k2].numpy().tobytes() == wg[1].tobytes(), (r, k1)
 
 
 def test_shard_ranges_cover_and_balance():

@@ -32,6 +32,12 @@ def test_world1_cuda_engine_matches_oracle(cuda_lib, device):
     assert_forward_exact(tuple(t.detach().cpu().numpy() for t in (d1, d2, i1, i2)), want)
     wg = oracle.backward(x1.numpy(), x2.numpy(), gd1.numpy(), gd2.numpy(), want[2], want[3])
     assert_grad_close((a.grad.cpu().numpy(), c.grad.cpu().numpy()), wg)
+    # deterministic mode of the sharded path (replicated nnd_backward_exact_cuda_f32): every gradient bit
+    a2 = x1.to(device).requires_grad_(True)
+    c2 = x2.to(device).requires_grad_(True)
+    e1, e2, _, _ = sharded.nnd_sharded_with_idx(a2, c2, exact=True)
+    ((e1 * gd1.to(device)).sum() + (e2 * gd2.to(device)).sum()).backward()
+    assert a2.grad.cpu().numpy().tobytes() == wg[0].tobytes() and c2.grad.cpu().numpy().tobytes() == wg[1].tobytes()
 
 
 @pytest.mark.parametrize("kind,b,n,m,cuts", [
