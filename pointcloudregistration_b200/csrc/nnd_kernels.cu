@@ -859,6 +859,19 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   const int grid = yp.total_units < grid_full ? (int)yp.total_units : grid_full;
   const size_t smem = sizeof(SymStage<kTT>) * kStages + (size_t)si.threads * si.qpt * 8;  // ring + row bookkeeping
   const bool panels = shape == kShapeLarge && nrows >= panel_min_rows();
+  // Tuning experiment, off by default: NND_B200_SYM_SEED=1 runs the panel path's filter seed in
+  // front of the persistent kernel as well (fewer column slow-path entries on mid-sized clouds for ~ TT / rows extra work).
+  static const int sym_seed = getenv("NND_B200_SYM_SEED") ? atoi(getenv("NND_B200_SYM_SEED")) : 0;
+  if (!panels && sym_seed > 0 && shape == kShapeLarge) {
+    const int t_first = (row_lo + kTT - 1) / kTT;
+    int ns = row_hi / kTT - t_first;
+    ns = ns > sym_seed ? sym_seed : ns;
+    if (ns > 0) {
+      dim3 g((unsigned)((n2 + 511) / 512), (unsigned)b);
+      nnd_seed_filter_kernel<kTT><<<g, 256, 0, st>>>(c2, soa1, cdist, n2, yp.ttiles, yp.qtiles, t_first, ns, 1.0f, n2);
+      ++g_launches;
+    }
+  }
   if (panels) {
     SymCParams cp{};
     cp.qsoa = soa1;
