@@ -87,6 +87,50 @@ int nnd_forward_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int
                          float *dist1, float *dist2, int32_t *idx1, int32_t *idx2,
                          void *workspace, size_t workspace_bytes, void *stream);
 
+/* Which forward nnd_forward_cuda_f32 runs for clouds of n and m points:
+ *   0 = single-launch small-cloud kernel (both clouds <= nnd_small_max_points(); no workspace; 2*b*n*m evaluations),
+ *   1 = two-pass kernel (prepare + scan + finalize; 2*b*n*m evaluations),
+ *   2 = symmetric kernels (every distance evaluated once: b*n*m evaluations).  Results are bit-identical on all. */
+int nnd_forward_kind(int n, int m);
+
+/* Small clouds (the sizes the reference's callers really use: DIP patches B=256 x 256 points, dip/train.py:84; NDP
+ * clouds of ~3 k points, registration.py:236).  When both clouds have at most nnd_small_max_points() points the forward
+ * is ONE launch (whole target cloud in shared memory, index resolved in the same kernel, no workspace: pass NULL / 0)
+ * and the backward is ONE launch (gradients accumulated in shared memory, no memsets).  nnd_workspace_bytes and
+ * nnd_query_workspace_bytes return 0 for such shapes.  nnd_set_small_max_points(points >= 0) sets the limit and returns
+ * the previous one (negative: query only); default 4096, environment NND_B200_SMALL_MAX, hard maximum 16384. */
+int nnd_small_max_points(void);
+int nnd_set_small_max_points(int points);
+/* Tuning / test knob of the single-launch forward: warps per CTA (4, 8, 16), queries per lane (1, 2) and how many
+ * warps share one set of queries while splitting the target cloud between them (a divisor of warps).  (0, 0, 0)
+ * restores the default (chosen from the problem size).  Results are bit-identical for every setting. */
+int nnd_set_small_config(int warps, int qpt, int tsplit);
+
+/* Ragged batches: per-cloud valid lengths len1[b], len2[b] (int64 DEVICE arrays, NULL = all points), the
+ * `lengths1/lengths2` of pytorch3d's knn_points as c2p-net/deformationpyramid/model/loss.py:143-144 calls it.
+ * Neighbours are searched among the first len points of the other cloud only; rows at or past a cloud's length get
+ * dist = 0, idx = 0 (gradient 0); a cloud of length 0 gives dist = 0, idx = 0 for its partner (my_lib.cpp:9-10).
+ * Lengths are clamped to [0, n] by the kernel.  One launch each, whole batch.  Only for shapes with
+ * nnd_ragged_supported(n, m) == 1 (single-launch kernels: both clouds <= nnd_small_max_points()); otherwise
+ * NND_EINVAL and the caller loops over the batch.  nnd_backward_ragged / nnd_knn_backward_ragged OVERWRITE both
+ * gradients (zero init fused). */
+int nnd_ragged_supported(int n, int m);
+int nnd_forward_ragged_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int m,
+                                const long long *len1, const long long *len2,
+                                float *dist1, float *dist2, int32_t *idx1, int32_t *idx2, void *stream);
+int nnd_query_ragged_cuda_f32(const float *query, const float *target, int b, int nq, int nt,
+                              const long long *lenq, const long long *lent,
+                              float *dist, int32_t *idx, void *stream);
+int nnd_backward_ragged_cuda_f32(const float *xyz1, const float *xyz2,
+                                 const float *graddist1, const float *graddist2,
+                                 const int32_t *idx1, const int32_t *idx2, int b, int n, int m,
+                                 const long long *len1, const long long *len2,
+                                 float *gradxyz1, float *gradxyz2, void *stream);
+int nnd_knn_backward_ragged_cuda_f32(const float *query, const float *target, const float *graddist,
+                                     const int32_t *idx, int b, int nq, int nt,
+                                     const long long *lenq, const long long *lent,
+                                     float *grad_query, float *grad_target, void *stream);
+
 /* 1 when nnd_forward_cuda_f32 takes the symmetric kernel for clouds of n and m points (every distance evaluated
  * once: b*n*m evaluations per call), 0 when it takes the two-pass kernel (2*b*n*m evaluations; small clouds).
  * Results are bit-identical either way; bench.py uses this to count the work a launch executes. */
@@ -140,10 +184,15 @@ int nnd_backward_exact_cuda_f32(const float *xyz1, const float *xyz2,
  * DESIGN.md section 4.0).  Results are bit-identical.  Sets the threshold (rows > 0) and returns the previous value;
  * rows <= 0 only queries.  Default 200000, or the environment variable NND_B200_PANEL_MIN_ROWS. */
 long long nnd_set_panel_min_rows(long long rows);
-/* Which scan nnd_forward_rows_cuda_f32 runs for rows [row_lo, row_hi) of an [n]-point xyz1 against an [m]-point xyz2:
- * 1 = persistent symmetric kernel, 2 = panel kernel, 3 = panel kernel with the roles of the clouds swapped (ranges
- * shorter than m), 0 = nothing to do.  (nnd_forward_cuda_f32 = the full range when nnd_forward_is_symmetric(n, m).) */
-int nnd_rows_scan_kind(int n, int m, int row_lo, int row_hi);
+/* Which scan nnd_forward_rows_cuda_f32 runs for rows [row_lo, row_hi) of a [b, n]-point xyz1 against a [b, m]-point
+ * xyz2: 1 = persistent symmetric kernel, 2 = panel kernel, 3 = panel kernel with the roles of the clouds swapped
+ * (ranges shorter than m), 0 = nothing to do.  (nnd_forward_cuda_f32 = the full range when
+ * nnd_forward_is_symmetric(n, m).)  The same helper decides inside nnd_forward_rows_cuda_f32.  One exception: a call
+ * whose stream is being captured into a CUDA graph always takes the persistent kernel (results are bit-identical). */
+int nnd_rows_scan_kind(int b, int n, int m, int row_lo, int row_hi);
+/* Tuning knob: sample tiles (512 rows each) of the column-filter seed pass run in front of the PERSISTENT symmetric kernel
+ * (0 = off, the default; the panel scan always seeds).  Returns the previous value; negative only queries. */
+int nnd_set_sym_seed_tiles(int tiles);
 /* Column tiles (512 points) per panel launch: 0 = chosen from the row count (default), 1, 2 or 4 = forced.  Returns the
  * previous setting; other values only query.  Environment: NND_B200_PANEL_TILES. */
 int nnd_set_panel_tiles(int tiles);

@@ -45,7 +45,21 @@ SIGNATURES = {
     "nnd_last_launch_count": (c_int, []),
     "nnd_set_panel_min_rows": (c_longlong, [c_longlong]),
     "nnd_set_panel_tiles": (c_int, [c_int]),
-    "nnd_rows_scan_kind": (c_int, [c_int, c_int, c_int, c_int]),
+    "nnd_rows_scan_kind": (c_int, [c_int, c_int, c_int, c_int, c_int]),
+    "nnd_set_sym_seed_tiles": (c_int, [c_int]),
+    "nnd_forward_kind": (c_int, [c_int, c_int]),
+    "nnd_small_max_points": (c_int, []),
+    "nnd_set_small_max_points": (c_int, [c_int]),
+    "nnd_set_small_config": (c_int, [c_int, c_int, c_int]),
+    "nnd_ragged_supported": (c_int, [c_int, c_int]),
+    "nnd_forward_ragged_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                             c_void_p, c_void_p, c_void_p, c_void_p]),
+    "nnd_query_ragged_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                           c_void_p, c_void_p]),
+    "nnd_backward_ragged_cuda_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                              c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "nnd_knn_backward_ragged_cuda_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p,
+                                                  c_void_p, c_void_p, c_void_p, c_void_p]),
     "nnd_chamfer_reduce_workspace_bytes": (c_size_t, []),
     "nnd_chamfer_reduce_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float, c_float, c_void_p,
                                              c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),

@@ -41,6 +41,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <atomic>
 #include <mutex>
 
 #include <cub/device/device_radix_sort.cuh>  // the deterministic backward sorts (neighbour row, own row) keys
@@ -428,6 +429,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
 // ----------------------------------------------------------------------------------
 #include "nnd_grad.cuh"
 #include "nnd_grad_exact.cuh"
+#include "nnd_small.cuh"
 
 // ----------------------------------------------------------------------------------
 // host side
@@ -493,23 +495,52 @@ struct DeviceInfo {
   int major = 0;
 };
 int device_info(DeviceInfo* out) {
+  // per-device cache, filled once under a mutex (calls may come from any host thread)
   static DeviceInfo cache[64];
+  static std::atomic<bool> ready[64];
+  static std::mutex mu;
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return (int)e;
   if (dev < 0 || dev >= 64) return NND_EINVAL;
-  if (cache[dev].sms == 0) {
-    int sms = 0, major = 0;
-    e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
-    if (e != cudaSuccess) return (int)e;
-    cache[dev].major = major;
-    cache[dev].sms = sms;
+  if (!ready[dev].load(std::memory_order_acquire)) {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ready[dev].load(std::memory_order_relaxed)) {
+      int sms = 0, major = 0;
+      e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      if (e != cudaSuccess) return (int)e;
+      e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+      if (e != cudaSuccess) return (int)e;
+      cache[dev].major = major;
+      cache[dev].sms = sms;
+      ready[dev].store(true, std::memory_order_release);
+    }
   }
   *out = cache[dev];
   return out->major == 10 ? 0 : NND_EDEVICE;
 }
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (kernel instantiation, device); thread-safe.
+struct SmemOptIn {
+  std::atomic<int> have[64];
+  SmemOptIn() {
+    for (auto& h : have) h.store(0);
+  }
+  template <typename K>
+  int ensure(K kern, size_t smem) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    dev &= 63;
+    if ((size_t)have[dev].load(std::memory_order_acquire) >= smem) return 0;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    int cur = have[dev].load();
+    while ((size_t)cur < smem && !have[dev].compare_exchange_weak(cur, (int)smem)) {
+    }
+    return 0;
+  }
+};
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 inline int tiles_of(int n) { return (n + kTT - 1) / kTT; }
@@ -533,11 +564,10 @@ constexpr int kReduceMaxBlocks = 1024;  // partial sums of nnd_chamfer_reduce_ke
 
 // NND_B200_DEBUG_SYNC=1: synchronise after every kernel of the forward and report it on stderr (triage aid).
 void debug_sync(const char* what, cudaStream_t st) {
-  static int on = -1;
-  if (on < 0) {
+  static const int on = [] {
     const char* e = getenv("NND_B200_DEBUG_SYNC");
-    on = (e && e[0] == '1') ? 1 : 0;
-  }
+    return (e && e[0] == '1') ? 1 : 0;
+  }();
   if (!on) return;
   fprintf(stderr, "[nnd] %s launched...\n", what);
   fflush(stderr);
@@ -555,14 +585,9 @@ inline unsigned grid_for(long long items, int sms) {
 template <int THREADS, int QPT, int MINB>
 int launch_sym(const SymParams& yp, int grid, size_t smem, cudaStream_t st) {
   auto kern = nnd_scan_sym_kernel<THREADS, QPT, kTT, kChunk, kStages, MINB>;
-  static bool attr_set[64] = {};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (!attr_set[dev & 63]) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    attr_set[dev & 63] = true;
-  }
+  static SmemOptIn optin;
+  int rc = optin.ensure(kern, smem);
+  if (rc) return rc;
   kern<<<grid, THREADS, smem, st>>>(yp);
   return 0;
 }
@@ -600,15 +625,32 @@ int panel_ctx(PanelCtx** out) {
 
 // Rows per launch below which the panel path does not pay (each launch must be long against its launch, copy and
 // ramp): NND_B200_PANEL_MIN_ROWS overrides (tests use 1 to push every symmetric scan through the panels).
-long long g_panel_min_rows = -1;
-int g_panel_tiles = -1;  // 0 = choose from the row count; 1, 2, 4 = forced (tests, tuning)
+// Tuning knobs are atomics: nnd_set_panel_* may be called while other host threads enqueue forwards.
+std::atomic<long long> g_panel_min_rows{-1};
+std::atomic<int> g_panel_tiles{-1};  // 0 = choose from the row count; 1, 2, 4 = forced (tests, tuning)
 long long panel_min_rows() {
-  if (g_panel_min_rows < 0) {
+  long long v = g_panel_min_rows.load(std::memory_order_relaxed);
+  if (v < 0) {
     const char* e = getenv("NND_B200_PANEL_MIN_ROWS");
-    g_panel_min_rows = e ? atoll(e) : 200000;
-    if (g_panel_min_rows < 1) g_panel_min_rows = 1;
+    long long init = e ? atoll(e) : 200000;
+    if (init < 1) init = 1;
+    long long expect = -1;
+    g_panel_min_rows.compare_exchange_strong(expect, init);  // somebody else's value (or a set) wins
+    v = g_panel_min_rows.load(std::memory_order_relaxed);
   }
-  return g_panel_min_rows;
+  return v;
+}
+int panel_tiles() {
+  int v = g_panel_tiles.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = getenv("NND_B200_PANEL_TILES");
+    int init = e ? atoi(e) : 0;
+    if (!(init == 1 || init == 2 || init == 4)) init = 0;
+    int expect = -1;
+    g_panel_tiles.compare_exchange_strong(expect, init);
+    v = g_panel_tiles.load(std::memory_order_relaxed);
+  }
+  return v;
 }
 
 // Shortest row range that takes the role-swapped panel path (each panel launch streams <= 2048 of its rows).
@@ -649,35 +691,40 @@ int scan_panels(const SymCParams& yp, const float* soa2, int b, int qblocks, int
   int rc = panel_ctx(&c);
   if (rc) return rc;
   cudaError_t e;
-  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-  if ((e = cudaStreamIsCapturing(st, &cap)) != cudaSuccess) return (int)e;
-  const bool capturing = cap != cudaStreamCaptureStatusNone;
   if ((e = cudaEventRecord(c->fork, st)) != cudaSuccess) return (int)e;
-  for (int i = 0; i < kPanelMaxBufs; ++i)
-    if ((e = cudaStreamWaitEvent(c->s[i], c->fork, 0)) != cudaSuccess) return (int)e;
+  // From here on the internal streams depend on `st`: whatever fails below, they are joined back into `st` before
+  // returning, so the caller's stream stays ordered after every kernel that reads the workspace and the constant
+  // window.  The first error is kept and returned after the join.
+  int first_err = 0;
+  auto keep = [&](cudaError_t x) {
+    if (x != cudaSuccess && first_err == 0) first_err = (int)x;
+  };
+  for (int i = 0; i < kPanelMaxBufs; ++i) keep(cudaStreamWaitEvent(c->s[i], c->fork, 0));
   // Scans enqueued from DIFFERENT caller streams share the constant window.  Buffer i is only ever written and read on
   // internal stream i, which orders scans with the same panel size; scans with different panel sizes cut the window
-  // differently, so every internal stream also waits for the whole previous scan.  (Not expressible while capturing:
-  // a captured scan is ordered by its own stream only, and graph replays must not overlap other panel scans.)
-  if (!capturing && c->have_done)
-    for (int i = 0; i < kPanelMaxBufs; ++i)
-      if ((e = cudaStreamWaitEvent(c->s[i], c->done, 0)) != cudaSuccess) return (int)e;
-  // launches in flight x CTAs per launch should cover the 2 * sms resident CTAs about twice
-  if (g_panel_tiles < 0) g_panel_tiles = getenv("NND_B200_PANEL_TILES") ? atoi(getenv("NND_B200_PANEL_TILES")) : 0;
-  int pt = qblocks * 2 >= 3 * sms ? 4 : qblocks * 4 >= 3 * sms ? 2 : 1;
-  if (g_panel_tiles == 1 || g_panel_tiles == 2 || g_panel_tiles == 4) pt = g_panel_tiles;
-  rc = pt == 4 ? scan_panels_pt<4>(yp, soa2, b, qblocks, c)
-     : pt == 2 ? scan_panels_pt<2>(yp, soa2, b, qblocks, c)
-               : scan_panels_pt<1>(yp, soa2, b, qblocks, c);
-  if (rc) return rc;
+  // differently, so every internal stream also waits for the whole previous scan.  (Panel scans are never captured
+  // into CUDA graphs: forward_rows_impl falls back to the persistent kernel while `st` is capturing, so every panel
+  // scan of the process passes through here and is ordered by these events.)
+  if (c->have_done)
+    for (int i = 0; i < kPanelMaxBufs; ++i) keep(cudaStreamWaitEvent(c->s[i], c->done, 0));
+  if (first_err == 0) {
+    // launches in flight x CTAs per launch should cover the 2 * sms resident CTAs about twice
+    int pt = qblocks * 2 >= 3 * sms ? 4 : qblocks * 4 >= 3 * sms ? 2 : 1;
+    const int forced = panel_tiles();
+    if (forced == 1 || forced == 2 || forced == 4) pt = forced;
+    rc = pt == 4 ? scan_panels_pt<4>(yp, soa2, b, qblocks, c)
+       : pt == 2 ? scan_panels_pt<2>(yp, soa2, b, qblocks, c)
+                 : scan_panels_pt<1>(yp, soa2, b, qblocks, c);
+    if (rc && first_err == 0) first_err = rc;
+  }
   for (int i = 0; i < kPanelMaxBufs; ++i) {
-    if ((e = cudaEventRecord(c->join[i], c->s[i])) != cudaSuccess) return (int)e;
-    if ((e = cudaStreamWaitEvent(st, c->join[i], 0)) != cudaSuccess) return (int)e;
+    keep(cudaEventRecord(c->join[i], c->s[i]));
+    keep(cudaStreamWaitEvent(st, c->join[i], 0));
   }
-  if (!capturing) {
-    if ((e = cudaEventRecord(c->done, st)) != cudaSuccess) return (int)e;
-    c->have_done = true;
-  }
+  e = cudaEventRecord(c->done, st);
+  keep(e);
+  c->have_done = e == cudaSuccess;  // a failed record leaves no stale event for the next scan to wait on
+  if (first_err) return first_err;
   return check_last(cudaGetLastError());
 }
 
@@ -687,6 +734,7 @@ void launch_scan(const ScanParams& sp, int grid, cudaStream_t st) {
 }
 
 inline bool use_symmetric(int n, int m);
+std::atomic<int> g_sym_seed{0};  // sample tiles of the filter seed in front of the persistent symmetric kernel (0 = off)
 // Shape of the symmetric kernel: the large one whenever the single-GPU entry point would pick the symmetric path
 // (more rows per warp step = fewer column slow paths); small clouds only get here through the row-range entry point.
 inline ScanShape sym_shape(int b, int n, int m, int sms) {
@@ -694,6 +742,20 @@ inline ScanShape sym_shape(int b, int n, int m, int sms) {
 }
 
 int scan_panels(const SymCParams& yp, const float* soa2, int b, int qblocks, int sms, cudaStream_t st);
+
+// The one place that decides which scan a row range takes; forward_rows_impl and nnd_rows_scan_kind both ask here.
+// While the caller's stream is being captured into a CUDA graph the persistent kernel is used whatever the size: the
+// panel scan keeps per-device state (the constant window and the events that order its users), which a graph replay
+// would bypass.  Results are bit-identical on every path.
+enum RowsPath { kRowsNone = 0, kRowsPersistent = 1, kRowsPanel = 2, kRowsSwapped = 3 };
+inline RowsPath rows_path(int b, int n, int m, int row_lo, int row_hi, int sms, bool capturing) {
+  const int nrows = row_hi - row_lo;
+  if (b <= 0 || n <= 0 || m <= 0 || nrows <= 0) return kRowsNone;
+  if (capturing) return kRowsPersistent;
+  if (nrows < m && m >= panel_min_rows() && m >= 2 * kTT && nrows >= panel_swap_min_rows()) return kRowsSwapped;
+  if (sym_shape(b, n, m, sms) == kShapeLarge && nrows >= panel_min_rows()) return kRowsPanel;
+  return kRowsPersistent;
+}
 
 // Role-swapped row range: when the range [row_lo, row_hi) of xyz1 is shorter than xyz2 (a rank's shard of the
 // multi-GPU path, or simply n < m), the panel scan runs with xyz2 in the registers and the RANGE as the streamed
@@ -798,8 +860,11 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   if (((uintptr_t)workspace & 255u) != 0) return NND_EWORKSPACE;
   const size_t need = rows_need(b, n1, n2);
   if (workspace_bytes < need) return NND_EWORKSPACE;
-  if (row_hi - row_lo > 0 && row_hi - row_lo < n2 && n2 >= panel_min_rows() && n2 >= 2 * kTT &&
-      row_hi - row_lo >= panel_swap_min_rows())
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  cudaError_t ce = cudaStreamIsCapturing(st, &cap);
+  if (ce != cudaSuccess) return (int)ce;
+  const RowsPath path = rows_path(b, n1, n2, row_lo, row_hi, di.sms, cap != cudaStreamCaptureStatusNone);
+  if (path == kRowsSwapped)
     return forward_rows_swapped_impl(c1, n1, c2, n2, b, row_lo, row_hi, dist1, idx1, colkeys, workspace, di, ev, st);
   char* w = (char*)workspace;
   float* soa1 = (float*)w;
@@ -858,10 +923,10 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   const int grid_full = di.sms * si.minb;
   const int grid = yp.total_units < grid_full ? (int)yp.total_units : grid_full;
   const size_t smem = sizeof(SymStage<kTT>) * kStages + (size_t)si.threads * si.qpt * 8;  // ring + row bookkeeping
-  const bool panels = shape == kShapeLarge && nrows >= panel_min_rows();
-  // Tuning experiment, off by default: NND_B200_SYM_SEED=1 runs the panel path's filter seed in
-  // front of the persistent kernel as well (fewer column slow-path entries on mid-sized clouds for ~ TT / rows extra work).
-  static const int sym_seed = getenv("NND_B200_SYM_SEED") ? atoi(getenv("NND_B200_SYM_SEED")) : 0;
+  const bool panels = path == kRowsPanel;
+  // Tuning knob (nnd_set_sym_seed_tiles): run the panel path's filter seed in front of the
+  // persistent kernel as well (fewer column slow-path entries on mid-sized clouds for ~ TT / rows extra work).
+  const int sym_seed = g_sym_seed.load(std::memory_order_relaxed);
   if (!panels && sym_seed > 0 && shape == kShapeLarge) {
     const int t_first = (row_lo + kTT - 1) / kTT;
     int ns = row_hi / kTT - t_first;
@@ -890,8 +955,7 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
       int ns = row_hi / kTT - t_first;
       const int want = nrows >= 500000 ? 4 : nrows >= 200000 ? 2 : 1;
       ns = ns > want ? want : ns;
-      static const int dbg_noseed = getenv("NND_B200_PANEL_NOSEED") ? 1 : 0;  // diagnosis only
-      if (ns > 0 && !dbg_noseed) {
+      if (ns > 0) {
         dim3 g((unsigned)((n2 + 511) / 512), (unsigned)b);
         nnd_seed_filter_kernel<kTT><<<g, 256, 0, st>>>(c2, soa1, cdist, n2, yp.ttiles, yp.qtiles, t_first, ns, 1.0f, n2);
         ++g_launches;
@@ -1025,6 +1089,136 @@ int twopass_impl(const float* q, int nq, const float* t, int nt, int b, int ndir
 // two-pass kernel (twice the arithmetic, no bookkeeping).
 inline bool use_symmetric(int n, int m) { return n >= 8192 && m >= 8192; }
 
+// ---- small clouds: single-launch forward / backward (nnd_small.cuh) ---------------------------------------------
+// Clouds of at most this many points (both of them) take nnd_small_kernel / nnd_grad_small_kernel.
+// NND_B200_SMALL_MAX overrides; nnd_set_small_max_points() is the run-time knob tests use to force either path.
+constexpr int kSmallHardMax = 16384;  // 3 * 16384 * 4 B = 192 KB of the 227 KB a CTA may have
+std::atomic<int> g_small_max{-1};
+int small_max_points() {
+  int v = g_small_max.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = getenv("NND_B200_SMALL_MAX");
+    int init = e ? atoi(e) : 4096;
+    init = init < 0 ? 0 : init > kSmallHardMax ? kSmallHardMax : init;
+    int expect = -1;
+    g_small_max.compare_exchange_strong(expect, init);
+    v = g_small_max.load(std::memory_order_relaxed);
+  }
+  return v;
+}
+inline bool use_small(int n, int m) { return (n > m ? n : m) <= small_max_points(); }
+// The shared-memory backward holds both gradients of a batch element: 12 B per point of both clouds.
+inline bool use_small_grad(int n, int m) { return use_small(n, m) && (long long)(n + m) * 12 <= 200 * 1024; }
+
+struct SmallCfg {
+  int warps, qpt, tsplit;
+};
+std::atomic<int> g_small_cfg{0};  // 0 = choose from the problem size; else warps << 16 | qpt << 8 | tsplit
+// total_q: queries of the whole launch; nq_max / nt_max: the larger cloud in the query / target role.
+SmallCfg small_config(long long total_q, int nq_max, int nt_max, int sms) {
+  const int forced = g_small_cfg.load(std::memory_order_relaxed);  // nnd_set_small_config: tests and tuning only
+  if (forced > 0) return SmallCfg{forced >> 16, (forced >> 8) & 0xff, forced & 0xff};
+  SmallCfg c;
+  // two queries per lane halve the shared-memory reads per pair; worth it once every scheduler still gets >= 2 warps
+  c.qpt = total_q >= (long long)sms * 4 * 2 * 64 ? 2 : 1;
+  const long long qwarps = (total_q + 32 * c.qpt - 1) / (32 * c.qpt);
+  const int chunks = (nt_max + kSmallChunk - 1) / kSmallChunk;
+  int ts = 1;  // split the targets over warps until the machine has ~2 warps per scheduler (each split keeps >= 2 chunks)
+  while (ts < 16 && qwarps * ts < 2ll * sms * 4 && chunks / (ts * 2) >= 2) ts *= 2;
+  c.tsplit = ts;
+  const int qgroups = (nq_max + 32 * c.qpt - 1) / (32 * c.qpt);  // query groups that cover the larger query cloud
+  c.warps = ts == 16 ? 16 : (long long)ts * qgroups <= 4 ? 4 : 8;
+  return c;
+}
+
+template <int WARPS, int QPT>
+int launch_small_t(const SmallParams& sp, int grid, size_t smem, cudaStream_t st) {
+  auto kern = nnd_small_kernel<WARPS, QPT>;
+  if (smem > 48 * 1024) {
+    static SmemOptIn optin;
+    int rc = optin.ensure(kern, smem);
+    if (rc) return rc;
+  }
+  kern<<<grid, WARPS * 32, smem, st>>>(sp);
+  return 0;
+}
+
+// ndir == 2: both directions (nnd_forward);  ndir == 1: cloud 0 queries cloud 1 only (nnd_query).
+int small_forward_impl(const float* c0, int n0, const float* c1, int n1, int b, int ndir, const long long* len0,
+                       const long long* len1, float* dist0, int32_t* idx0, float* dist1, int32_t* idx1,
+                       cudaStream_t st) {
+  cudaEvent_t* ev = nullptr;
+  if (g_prof.enabled && g_prof.used < kProfSlots) ev = &g_prof.ev[4 * g_prof.used++];
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  const long long total_q = (long long)b * (n0 + (ndir == 2 ? n1 : 0));
+  const int nq_max = ndir == 2 && n1 > n0 ? n1 : n0;
+  const int nt_max = ndir == 2 && n0 > n1 ? n0 : n1;
+  const SmallCfg cfg = small_config(total_q, nq_max, nt_max, di.sms);
+  const int qc = (cfg.warps / cfg.tsplit) * 32 * cfg.qpt;
+  SmallParams sp{};
+  sp.xyz[0] = c0;
+  sp.xyz[1] = c1;
+  sp.dist[0] = dist0;
+  sp.dist[1] = dist1;
+  sp.idx[0] = idx0;
+  sp.idx[1] = idx1;
+  sp.len[0] = len0;
+  sp.len[1] = len1;
+  sp.cnt[0] = n0;
+  sp.cnt[1] = n1;
+  sp.qblocks[0] = (n0 + qc - 1) / qc;
+  sp.qblocks[1] = ndir == 2 ? (n1 + qc - 1) / qc : 0;
+  sp.blocks0 = b * sp.qblocks[0];
+  sp.tsplit = cfg.tsplit;
+  sp.mp_max = (nt_max + kSmallChunk - 1) / kSmallChunk * kSmallChunk;
+  sp.one = 1.0f;
+  const long long grid = (long long)b * (sp.qblocks[0] + sp.qblocks[1]);
+  if (grid > 0x7fffffffLL) return NND_EINVAL;
+  const size_t smem = (size_t)3 * sp.mp_max * sizeof(float) + (cfg.tsplit > 1 ? (size_t)qc * 8 : 0);
+  if (ev) {
+    cudaEventRecord(ev[0], st);
+    cudaEventRecord(ev[1], st);
+  }
+  if (cfg.warps == 4 && cfg.qpt == 1) rc = launch_small_t<4, 1>(sp, (int)grid, smem, st);
+  else if (cfg.warps == 4) rc = launch_small_t<4, 2>(sp, (int)grid, smem, st);
+  else if (cfg.warps == 8 && cfg.qpt == 1) rc = launch_small_t<8, 1>(sp, (int)grid, smem, st);
+  else if (cfg.warps == 8) rc = launch_small_t<8, 2>(sp, (int)grid, smem, st);
+  else if (cfg.qpt == 1) rc = launch_small_t<16, 1>(sp, (int)grid, smem, st);
+  else rc = launch_small_t<16, 2>(sp, (int)grid, smem, st);
+  if (rc) return rc;
+  ++g_launches;
+  if (ev) {
+    cudaEventRecord(ev[2], st);
+    cudaEventRecord(ev[3], st);
+  }
+  debug_sync("small_forward", st);
+  return check_last(cudaGetLastError());
+}
+
+template <int THREADS>
+int launch_grad_small_t(const GradSmallParams& gp, int b, size_t smem, cudaStream_t st) {
+  auto kern = nnd_grad_small_kernel<THREADS>;
+  if (smem > 48 * 1024) {
+    static SmemOptIn optin;
+    int rc = optin.ensure(kern, smem);
+    if (rc) return rc;
+  }
+  kern<<<b, THREADS, smem, st>>>(gp);
+  return 0;
+}
+
+int small_backward_impl(const GradSmallParams& gp, int b, cudaStream_t st) {
+  const size_t smem = (size_t)3 * (gp.cnt[0] + gp.cnt[1]) * sizeof(float);
+  const int rc = gp.cnt[0] + gp.cnt[1] >= 2048 ? launch_grad_small_t<1024>(gp, b, smem, st)
+                                               : launch_grad_small_t<256>(gp, b, smem, st);
+  if (rc) return rc;
+  ++g_launches;
+  debug_sync("small_backward", st);
+  return check_last(cudaGetLastError());
+}
+
 int zero_outputs(float* dist, int32_t* idx, long long count, cudaStream_t st) {
   if (count <= 0) return 0;
   cudaError_t e = cudaMemsetAsync(dist, 0, (size_t)count * sizeof(float), st);
@@ -1069,6 +1263,7 @@ const char* nnd_error_string(int code) {
 
 size_t nnd_workspace_bytes(int b, int n, int m) {
   if (b <= 0 || n <= 0 || m <= 0) return 256;
+  if (use_small(n, m)) return 0;  // single-launch path: no workspace (the pointer may be null)
   return nnd_rows_workspace_bytes(b, n, m) + colkey_bytes(b, m);
 }
 
@@ -1084,18 +1279,44 @@ size_t nnd_colkeys_count(int b, int m) {
 
 int nnd_row_group(void) { return kRowAlign; }
 
-int nnd_forward_is_symmetric(int n, int m) { return use_symmetric(n, m) ? 1 : 0; }
+int nnd_forward_is_symmetric(int n, int m) { return !use_small(n, m) && use_symmetric(n, m) ? 1 : 0; }
 
-int nnd_rows_scan_kind(int n, int m, int row_lo, int row_hi) {
-  const int nrows = row_hi - row_lo;
-  if (n <= 0 || m <= 0 || nrows <= 0) return 0;
-  if (nrows < m && m >= panel_min_rows() && m >= 2 * kTT && nrows >= panel_swap_min_rows()) return 3;
-  if (nrows >= panel_min_rows() && use_symmetric(n, m)) return 2;
-  return 1;
+int nnd_forward_kind(int n, int m) { return use_small(n, m) ? 0 : use_symmetric(n, m) ? 2 : 1; }
+
+int nnd_small_max_points(void) { return small_max_points(); }
+
+int nnd_set_small_config(int warps, int qpt, int tsplit) {
+  if (warps == 0 && qpt == 0 && tsplit == 0) {
+    g_small_cfg.store(0);
+    return 0;
+  }
+  if (!(warps == 4 || warps == 8 || warps == 16) || !(qpt == 1 || qpt == 2) || tsplit < 1 || warps % tsplit != 0)
+    return NND_EINVAL;
+  g_small_cfg.store(warps << 16 | qpt << 8 | tsplit);
+  return 0;
+}
+
+int nnd_set_small_max_points(int points) {
+  const int before = small_max_points();
+  if (points >= 0) g_small_max.store(points > kSmallHardMax ? kSmallHardMax : points);
+  return before;
+}
+
+int nnd_rows_scan_kind(int b, int n, int m, int row_lo, int row_hi) {
+  DeviceInfo di;
+  const int sms = device_info(&di) == 0 ? di.sms : 148;  // callable without a device (tests, planning): B200 has 148 SMs
+  return (int)rows_path(b, n, m, row_lo, row_hi, sms, false);
+}
+
+int nnd_set_sym_seed_tiles(int tiles) {
+  const int before = g_sym_seed.load();
+  if (tiles >= 0) g_sym_seed.store(tiles > 64 ? 64 : tiles);
+  return before;
 }
 
 size_t nnd_query_workspace_bytes(int b, int nq, int nt) {
   if (b <= 0 || nq <= 0 || nt <= 0) return 256;
+  if (use_small(nq, nt)) return 0;
   return soa_bytes(b, nq) + soa_bytes(b, nt) + key_bytes(b, nq);
 }
 
@@ -1114,7 +1335,10 @@ int nnd_forward_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int
   if (b == 0 || (n == 0 && m == 0)) return 0;
   if (n == 0) return zero_outputs(dist2, idx2, (long long)b * m, st);  // my_lib.cpp:9-10,21-22 with an empty inner loop
   if (m == 0) return zero_outputs(dist1, idx1, (long long)b * n, st);
-  if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2 || !workspace) return NND_EINVAL;
+  if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2) return NND_EINVAL;
+  if (use_small(n, m))
+    return small_forward_impl(xyz1, n, xyz2, m, b, 2, nullptr, nullptr, dist1, idx1, dist2, idx2, st);
+  if (!workspace) return NND_EINVAL;
   if (workspace_bytes < nnd_workspace_bytes(b, n, m)) return NND_EWORKSPACE;
   if (!use_symmetric(n, m))
     return twopass_impl(xyz1, n, xyz2, m, b, 2, dist1, idx1, dist2, idx2, workspace, workspace_bytes, st);
@@ -1184,7 +1408,10 @@ int nnd_query_cuda_f32(const float* query, const float* target, int b, int nq, i
   cudaStream_t st = (cudaStream_t)stream;
   if (b == 0 || nq == 0) return 0;
   if (nt == 0) return zero_outputs(dist, idx, (long long)b * nq, st);
-  if (!query || !target || !dist || !idx || !workspace) return NND_EINVAL;
+  if (!query || !target || !dist || !idx) return NND_EINVAL;
+  if (use_small(nq, nt))
+    return small_forward_impl(query, nq, target, nt, b, 1, nullptr, nullptr, dist, idx, nullptr, nullptr, st);
+  if (!workspace) return NND_EINVAL;
   return twopass_impl(query, nq, target, nt, b, 1, dist, idx, nullptr, nullptr, workspace, workspace_bytes, st);
 }
 
@@ -1215,13 +1442,13 @@ int nnd_debug_sym_counters(unsigned long long* out2) {  // {slow-path entries, w
 
 long long nnd_set_panel_min_rows(long long rows) {
   const long long before = panel_min_rows();
-  if (rows > 0) g_panel_min_rows = rows;
+  if (rows > 0) g_panel_min_rows.store(rows);
   return before;
 }
 
 int nnd_set_panel_tiles(int tiles) {
-  const int before = g_panel_tiles < 0 ? 0 : g_panel_tiles;
-  if (tiles == 0 || tiles == 1 || tiles == 2 || tiles == 4) g_panel_tiles = tiles;
+  const int before = panel_tiles();
+  if (tiles == 0 || tiles == 1 || tiles == 2 || tiles == 4) g_panel_tiles.store(tiles);
   return before;
 }
 
@@ -1268,6 +1495,12 @@ int nnd_backward_cuda_f32(const float* xyz1, const float* xyz2, const float* gra
   cudaStream_t st = (cudaStream_t)stream;
   if (b == 0) return 0;
   if ((n > 0 && !gradxyz1) || (m > 0 && !gradxyz2)) return NND_EINVAL;
+  if (n > 0 && m > 0 && use_small_grad(n, m)) {  // one launch: zero-init, both terms and the stores
+    if (!xyz1 || !xyz2 || !graddist1 || !graddist2 || !idx1 || !idx2) return NND_EINVAL;
+    GradSmallParams sp{{xyz1, xyz2}, {graddist1, graddist2}, {idx1, idx2}, {gradxyz1, gradxyz2}, {nullptr, nullptr},
+                       {n, m}, 2};
+    return small_backward_impl(sp, b, st);
+  }
   cudaError_t e = cudaSuccess;  // zero-init fused into the call (my_lib.cpp:91-94)
   if (n > 0) e = cudaMemsetAsync(gradxyz1, 0, (size_t)b * n * 3 * sizeof(float), st);
   if (m > 0 && e == cudaSuccess) e = cudaMemsetAsync(gradxyz2, 0, (size_t)b * m * 3 * sizeof(float), st);
@@ -1279,6 +1512,60 @@ int nnd_backward_cuda_f32(const float* xyz1, const float* xyz2, const float* gra
   gp.t[0] = GradTerm{xyz1, xyz2, graddist1, idx1, gradxyz1, gradxyz2, n, m, (long long)b * n};
   gp.t[1] = GradTerm{xyz2, xyz1, graddist2, idx2, gradxyz2, gradxyz1, m, n, (long long)b * m};
   return launch_grad(gp, st);
+}
+
+// ---- ragged batches (per-cloud lengths), single-launch kernels only
+int nnd_ragged_supported(int n, int m) { return use_small_grad(n, m) ? 1 : 0; }
+
+int nnd_forward_ragged_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int m, const long long* len1,
+                                const long long* len2, float* dist1, float* dist2, int32_t* idx1, int32_t* idx2,
+                                void* stream) {
+  g_launches = 0;
+  if (!sizes_ok(b, n, m)) return NND_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (b == 0 || (n == 0 && m == 0)) return 0;
+  if (n == 0) return zero_outputs(dist2, idx2, (long long)b * m, st);
+  if (m == 0) return zero_outputs(dist1, idx1, (long long)b * n, st);
+  if (!use_small_grad(n, m)) return NND_EINVAL;
+  if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2) return NND_EINVAL;
+  return small_forward_impl(xyz1, n, xyz2, m, b, 2, len1, len2, dist1, idx1, dist2, idx2, st);
+}
+
+int nnd_query_ragged_cuda_f32(const float* query, const float* target, int b, int nq, int nt, const long long* lenq,
+                              const long long* lent, float* dist, int32_t* idx, void* stream) {
+  g_launches = 0;
+  if (b < 0 || nq < 0 || nt < 0) return NND_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (b == 0 || nq == 0) return 0;
+  if (nt == 0) return zero_outputs(dist, idx, (long long)b * nq, st);
+  if (!use_small_grad(nq, nt)) return NND_EINVAL;
+  if (!query || !target || !dist || !idx) return NND_EINVAL;
+  return small_forward_impl(query, nq, target, nt, b, 1, lenq, lent, dist, idx, nullptr, nullptr, st);
+}
+
+int nnd_backward_ragged_cuda_f32(const float* xyz1, const float* xyz2, const float* graddist1, const float* graddist2,
+                                 const int32_t* idx1, const int32_t* idx2, int b, int n, int m, const long long* len1,
+                                 const long long* len2, float* gradxyz1, float* gradxyz2, void* stream) {
+  g_launches = 0;
+  if (b < 0 || n <= 0 || m <= 0) return NND_EINVAL;
+  if (b == 0) return 0;
+  if (!use_small_grad(n, m)) return NND_EINVAL;
+  if (!xyz1 || !xyz2 || !graddist1 || !graddist2 || !idx1 || !idx2 || !gradxyz1 || !gradxyz2) return NND_EINVAL;
+  GradSmallParams sp{{xyz1, xyz2}, {graddist1, graddist2}, {idx1, idx2}, {gradxyz1, gradxyz2}, {len1, len2}, {n, m}, 2};
+  return small_backward_impl(sp, b, (cudaStream_t)stream);
+}
+
+int nnd_knn_backward_ragged_cuda_f32(const float* query, const float* target, const float* graddist, const int32_t* idx,
+                                     int b, int nq, int nt, const long long* lenq, const long long* lent,
+                                     float* grad_query, float* grad_target, void* stream) {
+  g_launches = 0;
+  if (b < 0 || nq <= 0 || nt <= 0) return NND_EINVAL;
+  if (b == 0) return 0;
+  if (!use_small_grad(nq, nt)) return NND_EINVAL;
+  if (!query || !target || !graddist || !idx || !grad_query || !grad_target) return NND_EINVAL;
+  GradSmallParams sp{{query, target}, {graddist, nullptr}, {idx, nullptr}, {grad_query, grad_target}, {lenq, lent},
+                     {nq, nt}, 1};
+  return small_backward_impl(sp, b, (cudaStream_t)stream);
 }
 
 size_t nnd_backward_exact_workspace_bytes(int b, int n, int m) {
