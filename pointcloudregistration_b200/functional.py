@@ -42,6 +42,25 @@ def _workspace(nbytes: int, device: torch.device) -> torch.Tensor:
     return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
 
 
+class _on_device:
+    """`with torch.cuda.device(dev)` only when dev is not already current: the guard costs several microseconds per
+    call, which is most of a small-cloud forward (DIP patches, NDP clouds)."""
+
+    __slots__ = ("guard",)
+
+    def __init__(self, dev: torch.device):
+        idx = dev.index
+        self.guard = None if idx is None or idx == torch.cuda.current_device() else torch.cuda.device(dev)
+
+    def __enter__(self):
+        if self.guard is not None:
+            self.guard.__enter__()
+
+    def __exit__(self, *exc):
+        if self.guard is not None:
+            self.guard.__exit__(*exc)
+
+
 def nnd_forward_raw(xyz1: torch.Tensor, xyz2: torch.Tensor):
     """dist1[B,N], dist2[B,M] float32 and idx1[B,N], idx2[B,M] int32; no autograd."""
     _check_clouds(xyz1, xyz2)
@@ -55,13 +74,114 @@ def nnd_forward_raw(xyz1: torch.Tensor, xyz2: torch.Tensor):
     dist2 = torch.empty(b, m, dtype=torch.float32, device=dev)
     idx1 = torch.empty(b, n, dtype=torch.int32, device=dev)
     idx2 = torch.empty(b, m, dtype=torch.int32, device=dev)
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         nbytes = lib.nnd_workspace_bytes(b, n, m)
-        ws = _workspace(nbytes, dev)
-        rc = lib.nnd_forward_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), b, n, m, dist1.data_ptr(), dist2.data_ptr(),
-                                      idx1.data_ptr(), idx2.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
-    _cabi.check(rc, "nnd_forward_cuda_f32")
+        if nbytes == 0:  # small clouds: one launch, no workspace (include/nnd_b200.h)
+            rc = lib.nnd_forward_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), b, n, m, dist1.data_ptr(),
+                                          dist2.data_ptr(), idx1.data_ptr(), idx2.data_ptr(), None, 0, _stream_ptr(dev))
+        else:
+            ws = _workspace(nbytes, dev)
+            rc = lib.nnd_forward_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), b, n, m, dist1.data_ptr(),
+                                          dist2.data_ptr(), idx1.data_ptr(), idx2.data_ptr(), ws.data_ptr(), ws.numel(),
+                                          _stream_ptr(dev))
+    if rc:
+        _cabi.check(rc, "nnd_forward_cuda_f32")
     return dist1, dist2, idx1, idx2
+
+
+def _len_ptr(lengths, b: int, dev):
+    """int64 device tensor of per-cloud lengths (kept alive by the caller) or None."""
+    if lengths is None:
+        return None
+    if lengths.dtype != torch.int64 or lengths.device != dev or lengths.shape != (b,):
+        lengths = lengths.to(device=dev, dtype=torch.int64).reshape(b)
+    return lengths.contiguous()
+
+
+def ragged_supported(n: int, m: int) -> bool:
+    """True when clouds of n and m points take the single-launch kernels, which handle per-cloud lengths themselves."""
+    return bool(_cabi.load().nnd_ragged_supported(int(n), int(m)))
+
+
+def nnd_forward_ragged_raw(xyz1, xyz2, len1=None, len2=None):
+    """Both directions with per-cloud valid lengths (int64 tensors [B] or None) in ONE launch for the whole batch
+    (include/nnd_b200.h: nnd_forward_ragged_cuda_f32).  Rows at or past a length come back as dist 0 / idx 0."""
+    _check_clouds(xyz1, xyz2)
+    lib = _cabi.load()
+    xyz1, xyz2 = xyz1.contiguous(), xyz2.contiguous()
+    b, n, _ = xyz1.shape
+    m = xyz2.size(1)
+    dev = xyz1.device
+    len1, len2 = _len_ptr(len1, b, dev), _len_ptr(len2, b, dev)
+    dist1 = torch.empty(b, n, dtype=torch.float32, device=dev)
+    dist2 = torch.empty(b, m, dtype=torch.float32, device=dev)
+    idx1 = torch.empty(b, n, dtype=torch.int32, device=dev)
+    idx2 = torch.empty(b, m, dtype=torch.int32, device=dev)
+    with _on_device(dev):
+        rc = lib.nnd_forward_ragged_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), b, n, m,
+                                             None if len1 is None else len1.data_ptr(),
+                                             None if len2 is None else len2.data_ptr(), dist1.data_ptr(),
+                                             dist2.data_ptr(), idx1.data_ptr(), idx2.data_ptr(), _stream_ptr(dev))
+    _cabi.check(rc, "nnd_forward_ragged_cuda_f32")
+    return dist1, dist2, idx1, idx2
+
+
+def nnd_query_ragged_raw(query, target, lenq=None, lent=None):
+    """One direction with per-cloud lengths, one launch (nnd_query_ragged_cuda_f32)."""
+    _check_clouds(query, target)
+    lib = _cabi.load()
+    query, target = query.contiguous(), target.contiguous()
+    b, nq, _ = query.shape
+    nt = target.size(1)
+    dev = query.device
+    lenq, lent = _len_ptr(lenq, b, dev), _len_ptr(lent, b, dev)
+    dist = torch.empty(b, nq, dtype=torch.float32, device=dev)
+    idx = torch.empty(b, nq, dtype=torch.int32, device=dev)
+    with _on_device(dev):
+        rc = lib.nnd_query_ragged_cuda_f32(query.data_ptr(), target.data_ptr(), b, nq, nt,
+                                           None if lenq is None else lenq.data_ptr(),
+                                           None if lent is None else lent.data_ptr(), dist.data_ptr(), idx.data_ptr(),
+                                           _stream_ptr(dev))
+    _cabi.check(rc, "nnd_query_ragged_cuda_f32")
+    return dist, idx
+
+
+def nnd_backward_ragged_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2, len1=None, len2=None):
+    """gradxyz1, gradxyz2 of the ragged forward, one launch (nnd_backward_ragged_cuda_f32); rows past a length get 0."""
+    lib = _cabi.load()
+    b, n, _ = xyz1.shape
+    m = xyz2.size(1)
+    dev = xyz1.device
+    len1, len2 = _len_ptr(len1, b, dev), _len_ptr(len2, b, dev)
+    graddist1 = graddist1.to(device=dev, dtype=torch.float32).contiguous()
+    graddist2 = graddist2.to(device=dev, dtype=torch.float32).contiguous()
+    g1, g2 = torch.empty_like(xyz1), torch.empty_like(xyz2)
+    with _on_device(dev):
+        rc = lib.nnd_backward_ragged_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), graddist1.data_ptr(),
+                                              graddist2.data_ptr(), idx1.data_ptr(), idx2.data_ptr(), b, n, m,
+                                              None if len1 is None else len1.data_ptr(),
+                                              None if len2 is None else len2.data_ptr(), g1.data_ptr(), g2.data_ptr(),
+                                              _stream_ptr(dev))
+    _cabi.check(rc, "nnd_backward_ragged_cuda_f32")
+    return g1, g2
+
+
+def nnd_knn_backward_ragged_raw(query, target, graddist, idx, lenq=None, lent=None):
+    """grad_query, grad_target of the one-direction ragged query, one launch (nnd_knn_backward_ragged_cuda_f32)."""
+    lib = _cabi.load()
+    b, nq, _ = query.shape
+    nt = target.size(1)
+    dev = query.device
+    lenq, lent = _len_ptr(lenq, b, dev), _len_ptr(lent, b, dev)
+    graddist = graddist.to(device=dev, dtype=torch.float32).contiguous()
+    gq, gt = torch.empty_like(query), torch.empty_like(target)
+    with _on_device(dev):
+        rc = lib.nnd_knn_backward_ragged_cuda_f32(query.data_ptr(), target.data_ptr(), graddist.data_ptr(),
+                                                  idx.data_ptr(), b, nq, nt, None if lenq is None else lenq.data_ptr(),
+                                                  None if lent is None else lent.data_ptr(), gq.data_ptr(),
+                                                  gt.data_ptr(), _stream_ptr(dev))
+    _cabi.check(rc, "nnd_knn_backward_ragged_cuda_f32")
+    return gq, gt
 
 
 def row_group() -> int:
@@ -129,10 +249,11 @@ def nnd_query_raw(query: torch.Tensor, target: torch.Tensor):
     dev = query.device
     dist = torch.empty(b, nq, dtype=torch.float32, device=dev)
     idx = torch.empty(b, nq, dtype=torch.int32, device=dev)
-    with torch.cuda.device(dev):
-        ws = _workspace(lib.nnd_query_workspace_bytes(b, nq, nt), dev)
+    with _on_device(dev):
+        nbytes = lib.nnd_query_workspace_bytes(b, nq, nt)
+        ws = _workspace(nbytes, dev) if nbytes else None
         rc = lib.nnd_query_cuda_f32(query.data_ptr(), target.data_ptr(), b, nq, nt, dist.data_ptr(), idx.data_ptr(),
-                                    ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+                                    ws.data_ptr() if nbytes else None, ws.numel() if nbytes else 0, _stream_ptr(dev))
     _cabi.check(rc, "nnd_query_cuda_f32")
     return dist, idx
 
@@ -164,8 +285,12 @@ def nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2, exact=None):
     b, n, _ = xyz1.shape
     m = xyz2.size(1)
     dev = xyz1.device
-    graddist1 = graddist1.to(device=dev, dtype=torch.float32).contiguous()  # __init__.py:40-41
-    graddist2 = graddist2.to(device=dev, dtype=torch.float32).contiguous()
+    if graddist1.dtype != torch.float32 or graddist1.device != dev:
+        graddist1 = graddist1.to(device=dev, dtype=torch.float32)
+    if graddist2.dtype != torch.float32 or graddist2.device != dev:
+        graddist2 = graddist2.to(device=dev, dtype=torch.float32)
+    graddist1 = graddist1.contiguous()  # __init__.py:40-41 (an expanded mean-gradient is materialised here)
+    graddist2 = graddist2.contiguous()
     if graddist1.shape != (b, n) or graddist2.shape != (b, m):
         raise ValueError("graddist shapes must be [B,N] and [B,M]")
     if idx1.dtype != torch.int32 or idx2.dtype != torch.int32:
@@ -176,7 +301,7 @@ def nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2, exact=None):
     gradxyz2 = torch.empty_like(xyz2)
     if exact is None:
         exact = exact_backward_enabled()
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         if exact:
             nbytes = lib.nnd_backward_exact_workspace_bytes(b, n, m)
             if nbytes == 0:
@@ -191,7 +316,8 @@ def nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2, exact=None):
         rc = lib.nnd_backward_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), graddist1.data_ptr(), graddist2.data_ptr(),
                                        idx1.data_ptr(), idx2.data_ptr(), b, n, m, gradxyz1.data_ptr(),
                                        gradxyz2.data_ptr(), _stream_ptr(dev))
-    _cabi.check(rc, "nnd_backward_cuda_f32")
+    if rc:
+        _cabi.check(rc, "nnd_backward_cuda_f32")
     return gradxyz1, gradxyz2
 
 

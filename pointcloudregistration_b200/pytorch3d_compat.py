@@ -31,12 +31,20 @@ from .functional import _check_clouds, _stream_ptr, nnd_backward_raw, nnd_forwar
 _KNN = namedtuple("KNN", "dists idx knn")
 
 
-def _lengths(points: torch.Tensor, lengths: Optional[torch.Tensor], name: str) -> Optional[list]:
-    """None when every cloud uses all P points, else the per-cloud lengths as a python list."""
+def _lengths(points: torch.Tensor, lengths: Optional[torch.Tensor], name: str) -> Optional[torch.Tensor]:
+    """The per-cloud lengths as given (a tensor [N]) or None.  No host read here: shapes that take the single-launch
+    kernels hand the tensor to the kernel as it is (the kernel clamps every length to [0, P])."""
     if lengths is None:
         return None
     if lengths.ndim != 1 or lengths.shape[0] != points.shape[0]:
         raise ValueError(f"Expected {name} to be of shape (N,)")  # loss.py:44-47
+    return lengths
+
+
+def _length_list(points: torch.Tensor, lengths: Optional[torch.Tensor], name: str) -> Optional[list]:
+    """Host copy of the lengths for the per-cloud loop (large ragged clouds only): None when every cloud is full."""
+    if lengths is None:
+        return None
     vals = [int(v) for v in lengths.tolist()]
     if any(v < 0 or v > points.shape[1] for v in vals):
         raise ValueError(f"{name} must lie in [0, P]")
@@ -55,6 +63,11 @@ def _backward_term(q, t, gd, idx, grad_q, grad_t) -> None:
     _cabi.check(rc, "nnd_backward_term_cuda_f32")
 
 
+def _one_launch(p1, p2) -> bool:
+    """Ragged batches of this shape are handled by ONE launch for the whole batch (nnd_*_ragged_cuda_f32)."""
+    return p1.size(0) > 0 and p1.size(1) > 0 and p2.size(1) > 0 and F_.ragged_supported(p1.size(1), p2.size(1))
+
+
 class _KNN1Function(Function):
     """One direction, K = 1: dists [N,P1] f32 (squared), idx [N,P1] int32; rows >= lengths1[i] are 0."""
 
@@ -62,13 +75,18 @@ class _KNN1Function(Function):
     def forward(ctx, p1, p2, len1, len2):
         _check_clouds(p1, p2)
         p1c, p2c = p1.contiguous(), p2.contiguous()
+        ctx.one_launch = False
         if len1 is None and len2 is None:
             dists, idx = nnd_query_raw(p1c, p2c)
+        elif _one_launch(p1c, p2c):
+            ctx.one_launch = True
+            dists, idx = F_.nnd_query_ragged_raw(p1c, p2c, len1, len2)
         else:
+            len1, len2 = _length_list(p1c, len1, "lengths1"), _length_list(p2c, len2, "lengths2")
             n = p1c.size(0)
             dists = p1c.new_zeros(n, p1c.size(1))
             idx = torch.zeros(n, p1c.size(1), dtype=torch.int32, device=p1c.device)
-            for i in range(n):  # ragged batch: one launch per cloud on its valid prefix
+            for i in range(n):  # large ragged clouds: one forward per cloud on its valid prefix
                 l1 = p1c.size(1) if len1 is None else len1[i]
                 l2 = p2c.size(1) if len2 is None else len2[i]
                 if l1 == 0 or l2 == 0:
@@ -85,6 +103,9 @@ class _KNN1Function(Function):
         p1, p2, idx = ctx.saved_tensors
         len1, len2 = ctx.len1, ctx.len2
         gdists = gdists.to(torch.float32).contiguous()
+        if ctx.one_launch:
+            g1, g2 = F_.nnd_knn_backward_ragged_raw(p1, p2, gdists, idx, len1, len2)
+            return g1, g2, None, None
         g1, g2 = torch.zeros_like(p1), torch.zeros_like(p2)
         if len1 is None and len2 is None:
             _backward_term(p1, p2, gdists, idx, g1, g2)
@@ -103,15 +124,21 @@ class _KNN1Function(Function):
 
 class _NND2Function(Function):
     """Both directions, K = 1, with optional per-cloud lengths.  The homogeneous case is ONE symmetric
-    forward (every distance evaluated once, csrc/nnd_sym.cuh) instead of pytorch3d's two knn passes."""
+    forward (every distance evaluated once, csrc/nnd_sym.cuh) instead of pytorch3d's two knn passes; ragged batches
+    of small clouds are one launch too (per-cloud lengths read by the kernel, no host synchronisation)."""
 
     @staticmethod
     def forward(ctx, x, y, lx, ly):
         _check_clouds(x, y)
         xc, yc = x.contiguous(), y.contiguous()
+        ctx.one_launch = False
         if lx is None and ly is None:
             d1, d2, i1, i2 = nnd_forward_raw(xc, yc)
+        elif _one_launch(xc, yc):
+            ctx.one_launch = True
+            d1, d2, i1, i2 = F_.nnd_forward_ragged_raw(xc, yc, lx, ly)
         else:
+            lx, ly = _length_list(xc, lx, "x_lengths"), _length_list(yc, ly, "y_lengths")
             n = xc.size(0)
             d1, d2 = xc.new_zeros(n, xc.size(1)), yc.new_zeros(n, yc.size(1))
             i1 = torch.zeros(n, xc.size(1), dtype=torch.int32, device=xc.device)
@@ -133,6 +160,9 @@ class _NND2Function(Function):
         x, y, i1, i2 = ctx.saved_tensors
         lx, ly = ctx.lx, ctx.ly
         g1, g2 = g1.to(torch.float32).contiguous(), g2.to(torch.float32).contiguous()
+        if ctx.one_launch:
+            gx, gy = F_.nnd_backward_ragged_raw(x, y, g1, g2, i1, i2, lx, ly)
+            return gx, gy, None, None
         if lx is None and ly is None:
             gx, gy = nnd_backward_raw(x, y, g1, g2, i1, i2)
             return gx, gy, None, None
@@ -190,12 +220,12 @@ def _reduce(cham_x, cham_y, x_lengths, y_lengths, weights, batch_reduction, poin
     """Point and batch reductions of loss.py:185-215 (identical in pytorch3d's chamfer_distance)."""
     cham_x, cham_y = cham_x.sum(1), cham_y.sum(1)
     if point_reduction == "mean":
-        cham_x = cham_x / x_lengths.clamp(min=1)
-        cham_y = cham_y / y_lengths.clamp(min=1)
+        cham_x = cham_x / x_lengths  # loss.py:196-197: no clamp -- an empty cloud gives 0/0 = NaN there and here
+        cham_y = cham_y / y_lengths
     if batch_reduction is not None:
         cham_x, cham_y = cham_x.sum(), cham_y.sum()
         if batch_reduction == "mean":
-            div = weights.sum() if weights is not None else max(n, 1)
+            div = weights.sum() if weights is not None else n  # loss.py:210
             cham_x, cham_y = cham_x / div, cham_y / div
     return cham_x + cham_y
 
