@@ -429,7 +429,7 @@ def run_b200_arm(args, w):
         else:
             from pointcloudregistration_b200.sharded import shard_range
             lo, hi = shard_range(n, world, 0, align=lib.nnd_row_group()) if world > 1 else (0, n)
-            kind = lib.nnd_rows_scan_kind(n, m, lo, hi)
+            kind = lib.nnd_rows_scan_kind(b, n, m, lo, hi)
             scan_kernel_name = {1: "nnd_scan_sym_kernel",
                                 2: "nnd_scan_symc_kernel (one launch per panel of columns on rotating streams; the "
                                    "phase seed + all panel launches is timed as one)",

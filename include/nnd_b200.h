@@ -201,8 +201,8 @@ int nnd_set_panel_tiles(int tiles);
  * form registration.py:236 uses):  loss[0] = scale1 * sum(dist1 < trunc ? dist1 : 0) + scale2 * sum(dist2 < trunc ? dist2 : 0),
  * and, when the pointers are non-null, graddist1[i] = dist1[i] < trunc ? scale1 : 0 (likewise graddist2): d loss / d dist,
  * ready for nnd_backward_cuda_f32.  Deterministic (fixed summation order).  `workspace` is
- * nnd_chamfer_reduce_workspace_bytes() of 256-byte aligned device memory that the caller ZEROES ONCE; the kernel
- * leaves it ready for the next call. */
+ * nnd_chamfer_reduce_workspace_bytes() of 256-byte aligned device memory; it needs no initialisation and carries no
+ * state between calls (any scratch will do, e.g. a fresh allocation per call). */
 size_t nnd_chamfer_reduce_workspace_bytes(void);
 int nnd_chamfer_reduce_cuda_f32(const float *dist1, const float *dist2, int b, int n, int m,
                                 float trunc, float scale1, float scale2,

@@ -156,7 +156,7 @@ struct ReduceParams {
   float trunc;
   float* loss;       // [1]
   double* partial;   // [gridDim.x]
-  unsigned* ticket;  // [1], zero before the launch; reset by the kernel
+  unsigned* ticket;  // [1], zeroed by the launcher on the same stream when there is more than one block
 };
 
 __global__ void __launch_bounds__(256) nnd_chamfer_reduce_kernel(ReduceParams p) {
@@ -184,7 +184,7 @@ __global__ void __launch_bounds__(256) nnd_chamfer_reduce_kernel(ReduceParams p)
     for (int w = 0; w < 8; ++w) s += warp_sum[w];
     p.partial[blockIdx.x] = s;
     __threadfence();
-    last = atomicAdd(p.ticket, 1u) == gridDim.x - 1;
+    last = gridDim.x == 1 || atomicAdd(p.ticket, 1u) == gridDim.x - 1;  // one block: no ticket at all
   }
   __syncthreads();
   if (last && threadIdx.x == 0) {
@@ -192,6 +192,5 @@ __global__ void __launch_bounds__(256) nnd_chamfer_reduce_kernel(ReduceParams p)
     double s = 0.0;
     for (unsigned b = 0; b < gridDim.x; ++b) s += reinterpret_cast<volatile double*>(p.partial)[b];
     *p.loss = (float)s;
-    *p.ticket = 0u;  // ready for the next launch (and for CUDA-graph replays)
   }
 }

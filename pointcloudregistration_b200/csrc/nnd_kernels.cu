@@ -1476,12 +1476,16 @@ int nnd_chamfer_reduce_cuda_f32(const float* dist1, const float* dist2, int b, i
   rp.scale[1] = scale2;
   rp.trunc = trunc;
   rp.loss = loss;
-  rp.ticket = (unsigned*)workspace;  // first 256 bytes: the ticket (the caller zeroes the workspace once)
+  rp.ticket = (unsigned*)workspace;  // first 256 bytes: the ticket
   rp.partial = (double*)((char*)workspace + 256);
   const long long most = rp.count[0] > rp.count[1] ? rp.count[0] : rp.count[1];
-  long long blocks = (most + 255) / 256;
+  // clouds of up to 8192 points (the NDP loop's real size is ~3 k): ONE block, no ticket, no cross-call state
+  long long blocks = most <= 8192 ? 1 : (most + 1023) / 1024;
   if (blocks > kReduceMaxBlocks) blocks = kReduceMaxBlocks;
-  if (blocks < 1) blocks = 1;
+  if (blocks > 1) {  // the ticket is zeroed here, on the same stream: the workspace needs no preparation by the caller
+    cudaError_t e = cudaMemsetAsync(rp.ticket, 0, sizeof(unsigned), st);
+    if (e != cudaSuccess) return (int)e;
+  }
   nnd_chamfer_reduce_kernel<<<(unsigned)blocks, 256, 0, st>>>(rp);
   ++g_launches;
   return check_last(cudaGetLastError());

@@ -322,9 +322,10 @@ def nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2, exact=None):
 
 
 def chamfer_reduce_workspace(device) -> torch.Tensor:
-    """Zeroed scratch for chamfer_reduce_raw; allocate once and reuse (the kernel leaves it zeroed)."""
+    """Scratch for chamfer_reduce_raw: uninitialised and stateless (the launcher prepares what it needs on the
+    stream), so a fresh allocation per call is fine and nothing is shared between streams or graph captures."""
     lib = _cabi.load()
-    return torch.zeros(lib.nnd_chamfer_reduce_workspace_bytes(), dtype=torch.uint8, device=device)
+    return torch.empty(lib.nnd_chamfer_reduce_workspace_bytes(), dtype=torch.uint8, device=device)
 
 
 def chamfer_reduce_raw(dist1, dist2, trunc: float, scale1: float, scale2: float, loss, graddist1, graddist2, ws):
@@ -338,7 +339,7 @@ def chamfer_reduce_raw(dist1, dist2, trunc: float, scale1: float, scale2: float,
     for t in (dist1, dist2, loss, graddist1, graddist2):
         if t is not None and (t.dtype != torch.float32 or not t.is_contiguous() or t.device != dev):
             raise ValueError("chamfer_reduce_raw wants contiguous float32 tensors on one device")
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         rc = lib.nnd_chamfer_reduce_cuda_f32(dist1.data_ptr(), dist2.data_ptr(), b, n, m, float(trunc), float(scale1),
                                              float(scale2), loss.data_ptr(),
                                              graddist1.data_ptr() if graddist1 is not None else None,

@@ -243,9 +243,6 @@ def _full_lengths(points, lengths):
     return lengths.to(device=points.device, dtype=torch.int64)
 
 
-_reduce_ws = {}  # (device, stream) -> zeroed scratch of the fused epilogue (the kernel hands it back zeroed)
-
-
 class _FusedChamferFunction(Function):
     """Dense, unweighted chamfer with scalar output: nnd forward + ONE fused launch for mask, both reductions and
     d loss/d dist (nnd_chamfer_reduce_cuda_f32); the backward scales the saved d loss/d dist and runs nnd's backward.
@@ -255,10 +252,7 @@ class _FusedChamferFunction(Function):
     def forward(ctx, x, y, trunc, s1, s2):
         xc, yc = x.detach().contiguous(), y.detach().contiguous()  # dtype/device checked by nnd_forward_raw
         d1, d2, i1, i2 = F_.nnd_forward_raw(xc, yc)
-        key = (xc.device, torch.cuda.current_stream(xc.device).cuda_stream)
-        ws = _reduce_ws.get(key)
-        if ws is None:
-            ws = _reduce_ws[key] = F_.chamfer_reduce_workspace(xc.device)
+        ws = F_.chamfer_reduce_workspace(xc.device)  # per call: stateless scratch, nothing cached across streams
         loss = torch.empty((), dtype=torch.float32, device=xc.device)
         gd1, gd2 = torch.empty_like(d1), torch.empty_like(d2)
         F_.chamfer_reduce_raw(d1, d2, trunc, s1, s2, loss, gd1, gd2, ws)

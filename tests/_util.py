@@ -11,6 +11,8 @@ GOLDEN = Path(__file__).resolve().parent / "golden"
 DIGESTS = json.loads((GOLDEN / "digests.json").read_text())
 NPZ_CASES = sorted(k for k, v in DIGESTS.items() if v["stored"] == "npz")
 DIGEST_CASES = sorted(k for k, v in DIGESTS.items() if v["stored"] == "digest")
+# full-size configs (C2-C5): digests of the WHOLE output tensors of the compiled reference (make_golden_full.py)
+FULL_DIGESTS = json.loads((GOLDEN / "digests_full.json").read_text())
 
 # gradient tolerance north_star states: 1e-5 relative (summation order of the atomics differs)
 GRAD_RTOL = 1e-5

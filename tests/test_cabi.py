@@ -47,7 +47,19 @@ def test_workspace_size_formula(cuda_lib):
     # the row-range entry point keeps the column keys in a caller-owned buffer (they are all-reduced)
     assert cuda_lib.nnd_rows_workspace_bytes(1, 1_000_000, 1_000_000) + 8 * cuda_lib.nnd_colkeys_count(1, 1_000_000) <= w
     assert cuda_lib.nnd_colkeys_count(3, 513) == 3 * 1024 and cuda_lib.nnd_row_group() == 8
-    assert cuda_lib.nnd_query_workspace_bytes(2, 512, 512) == 2 * (2 * 512 * 12) + 2 * 512 * 8
+    assert cuda_lib.nnd_query_workspace_bytes(2, 5120, 5120) == 2 * (2 * 5120 * 12) + 2 * 5120 * 8
+    # small clouds take the single-launch kernels: no workspace at all
+    assert cuda_lib.nnd_small_max_points() == 4096
+    assert cuda_lib.nnd_workspace_bytes(256, 256, 256) == 0 and cuda_lib.nnd_query_workspace_bytes(2, 512, 512) == 0
+    assert cuda_lib.nnd_forward_kind(256, 256) == 0 and cuda_lib.nnd_forward_kind(4096, 4097) == 1
+    assert cuda_lib.nnd_forward_kind(16384, 16384) == 2 and cuda_lib.nnd_ragged_supported(3000, 2900) == 1
+    before = cuda_lib.nnd_set_small_max_points(0)
+    try:
+        assert cuda_lib.nnd_workspace_bytes(1, 256, 256) > 0 and cuda_lib.nnd_forward_kind(256, 256) == 1
+    finally:
+        cuda_lib.nnd_set_small_max_points(before)
+    assert cuda_lib.nnd_set_small_config(8, 3, 1) == 10001 and cuda_lib.nnd_set_small_config(8, 2, 3) == 10001
+    assert cuda_lib.nnd_set_small_config(0, 0, 0) == 0
 
 
 def test_argument_validation_needs_no_gpu(cuda_lib):
@@ -71,8 +83,9 @@ def test_forward_kernel_sass_is_bit_exact_form():
         pytest.skip("cuobjdump not available")
     kernels = re.split(r"Function : ", out.stdout)
     scan = [k for k in kernels if any(name in k.split("\n", 1)[0]
-                                      for name in ("nnd_scan_kernel", "nnd_scan_sym_kernel", "nnd_scan_symc_kernel"))]
-    assert len(scan) >= 2, "nnd_scan_kernel / nnd_scan_sym_kernel not found in the cubin"
+                                      for name in ("nnd_scan_kernel", "nnd_scan_sym_kernel", "nnd_scan_symc_kernel",
+                                                   "nnd_small_kernel"))]
+    assert len(scan) >= 3 + 3 + 6 + 6, "a forward kernel instantiation is missing from the cubin"
     for k in scan:
         ops = re.findall(r"^\s+/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", k, flags=re.M)
         n = {name: sum(1 for o in ops if o.split(".")[0] == name) for name in ("FFMA", "FMUL2", "FADD2", "FFMA2", "FMNMX3")}
@@ -110,16 +123,19 @@ def test_scan_kind_selection_needs_no_gpu(cuda_lib):
     the roles of the clouds swapped."""
     k = cuda_lib.nnd_rows_scan_kind
     assert cuda_lib.nnd_set_panel_min_rows(0) == 200000            # query only
-    assert k(1_000_000, 1_000_000, 0, 1_000_000) == 2              # C4, one GPU
-    assert k(1_000_000, 1_000_000, 125_000, 250_000) == 3          # C4, one of 8 ranks: shorter than xyz2 -> swapped
-    assert k(262_144, 262_144, 0, 262_144) == 2                    # C5
-    assert k(100_000, 100_000, 0, 100_000) == 1                    # C3
-    assert k(100_000, 1_000_000, 0, 100_000) == 3                  # N < M on one GPU
-    assert k(1_000_000, 100_000, 0, 1_000_000) == 2                # N > M: rows in registers as usual
-    assert k(16_384, 16_384, 0, 0) == 0
+    assert k(1, 1_000_000, 1_000_000, 0, 1_000_000) == 2              # C4, one GPU
+    assert k(1, 1_000_000, 1_000_000, 125_000, 250_000) == 3          # C4, one of 8 ranks: shorter than xyz2 -> swapped
+    assert k(1, 262_144, 262_144, 0, 262_144) == 2                    # C5
+    assert k(1, 100_000, 100_000, 0, 100_000) == 1                    # C3
+    assert k(1, 100_000, 1_000_000, 0, 100_000) == 3                  # N < M on one GPU
+    assert k(1, 1_000_000, 100_000, 0, 1_000_000) == 2                # N > M: rows in registers as usual
+    assert k(1, 16_384, 16_384, 0, 0) == 0
+    # a long range of a cloud against a SMALL one through the rows ABI: many (row block x tile) units -> the large shape
+    # -> panels, exactly what nnd_forward_rows_cuda_f32 does (the decision is one shared helper)
+    assert k(1, 300_000, 4096, 0, 300_000) == 2
     before = cuda_lib.nnd_set_panel_min_rows(1)
     try:
-        assert k(9000, 8200, 0, 9000) == 2 and k(9000, 30000, 0, 3000) == 3
+        assert k(1, 9000, 8200, 0, 9000) == 2 and k(1, 9000, 30000, 0, 3000) == 3
     finally:
         cuda_lib.nnd_set_panel_min_rows(before)
     assert cuda_lib.nnd_set_panel_tiles(3) == 0 and cuda_lib.nnd_set_panel_tiles(-1) == 0   # invalid values only query

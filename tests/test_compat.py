@@ -64,7 +64,8 @@ def _cpu_chamfer(x, y, lx, ly, trunc, weights, batch_reduction, point_reduction)
         cx, cy = cx * weights[:, None], cy * weights[:, None]
     sx, sy = cx.sum(1), cy.sum(1)
     if point_reduction == "mean":
-        sx, sy = sx / np.maximum(lx, 1), sy / np.maximum(ly, 1)
+        with np.errstate(invalid="ignore", divide="ignore"):
+            sx, sy = sx / lx, sy / ly  # loss.py:196-197 divides by the lengths as they are: empty cloud -> NaN
     if batch_reduction is not None:
         sx, sy = sx.sum(), sy.sum()
         if batch_reduction == "mean":

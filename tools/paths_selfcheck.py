@@ -61,7 +61,7 @@ keys = None
 rows_d, rows_i = [], []
 for lo, hi in zip(cuts[:-1], cuts[1:]):
     d, i, k = F.nnd_forward_rows_raw(x1, x2, lo, hi)
-    say(f"rows [{lo},{hi}) scan kind {lib.nnd_rows_scan_kind(n, m, lo, hi)} ok")
+    say(f"rows [{lo},{hi}) scan kind {lib.nnd_rows_scan_kind(1, n, m, lo, hi)} ok")
     rows_d.append(d)
     rows_i.append(i)
     keys = k if keys is None else torch.minimum(keys, k)
