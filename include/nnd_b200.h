@@ -87,16 +87,18 @@ int nnd_forward_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int
                          float *dist1, float *dist2, int32_t *idx1, int32_t *idx2,
                          void *workspace, size_t workspace_bytes, void *stream);
 
-/* Which forward nnd_forward_cuda_f32 runs for clouds of n and m points:
- *   0 = single-launch small-cloud kernel (both clouds <= nnd_small_max_points(); no workspace; 2*b*n*m evaluations),
+/* Which forward nnd_forward_cuda_f32 runs for a batch of b cloud pairs of n and m points:
+ *   0 = single-launch small-cloud kernel (no workspace; 2*b*n*m evaluations): both clouds <= nnd_small_max_points(),
+ *       or -- a lone pair, where the general path cannot fill the machine -- up to 2.5x that with b*max(n,m) <= 3x that,
  *   1 = two-pass kernel (prepare + scan + finalize; 2*b*n*m evaluations),
  *   2 = symmetric kernels (every distance evaluated once: b*n*m evaluations).  Results are bit-identical on all. */
-int nnd_forward_kind(int n, int m);
+int nnd_forward_kind(int b, int n, int m);
 
 /* Small clouds (the sizes the reference's callers really use: DIP patches B=256 x 256 points, dip/train.py:84; NDP
  * clouds of ~3 k points, registration.py:236).  When both clouds have at most nnd_small_max_points() points the forward
  * is ONE launch (whole target cloud in shared memory, index resolved in the same kernel, no workspace: pass NULL / 0)
- * and the backward is ONE launch (gradients accumulated in shared memory, no memsets).  nnd_workspace_bytes and
+ * and the backward is ONE launch (every CTA owns a range of gradient rows in shared memory: no memsets, no global
+ * atomics).  nnd_workspace_bytes and
  * nnd_query_workspace_bytes return 0 for such shapes.  nnd_set_small_max_points(points >= 0) sets the limit and returns
  * the previous one (negative: query only); default 4096, environment NND_B200_SMALL_MAX, hard maximum 16384. */
 int nnd_small_max_points(void);

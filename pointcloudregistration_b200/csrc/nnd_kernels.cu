@@ -1106,9 +1106,25 @@ int small_max_points() {
   }
   return v;
 }
-inline bool use_small(int n, int m) { return (n > m ? n : m) <= small_max_points(); }
-// The shared-memory backward holds both gradients of a batch element: 12 B per point of both clouds.
-inline bool use_small_grad(int n, int m) { return use_small(n, m) && (long long)(n + m) * 12 <= 200 * 1024; }
+// Measured crossover (profiles/r02_small_time.txt): up to 4096 points the single launch wins at every batch size; a
+// single cloud pair (b * points small) keeps winning up to ~10 k points, where the general path still runs at a
+// tenth of the machine (64 work units for 148 SMs).
+inline bool use_small(int b, int n, int m) {
+  const long long mx = n > m ? n : m, lim = small_max_points();
+  if (mx <= lim) return true;
+  const long long lim2 = lim * 5 / 2 < kSmallHardMax ? lim * 5 / 2 : kSmallHardMax;
+  return mx <= lim2 && (long long)b * mx <= lim * 3;
+}
+// Ragged batches and the one-launch backward key on the cloud sizes alone (no batch term): <= small_max_points().
+inline bool use_small_nm(int n, int m) { return (n > m ? n : m) <= small_max_points(); }
+// CTAs per batch element of the shared-memory backward: enough to put ~2 CTAs on every SM when the batch is small.
+inline int grad_small_parts(int b, int n, int m, int sms) {
+  long long parts = (2ll * sms + b - 1) / b;
+  const long long by_rows = ((long long)n + m) / 256;  // at least ~256 owned rows per CTA
+  if (parts > by_rows) parts = by_rows;
+  if (parts > 16) parts = 16;
+  return parts < 1 ? 1 : (int)parts;
+}
 
 struct SmallCfg {
   int warps, qpt, tsplit;
@@ -1198,21 +1214,27 @@ int small_forward_impl(const float* c0, int n0, const float* c1, int n1, int b, 
 }
 
 template <int THREADS>
-int launch_grad_small_t(const GradSmallParams& gp, int b, size_t smem, cudaStream_t st) {
+int launch_grad_small_t(const GradSmallParams& gp, long long grid, size_t smem, cudaStream_t st) {
   auto kern = nnd_grad_small_kernel<THREADS>;
   if (smem > 48 * 1024) {
     static SmemOptIn optin;
     int rc = optin.ensure(kern, smem);
     if (rc) return rc;
   }
-  kern<<<b, THREADS, smem, st>>>(gp);
+  kern<<<(unsigned)grid, THREADS, smem, st>>>(gp);
   return 0;
 }
 
-int small_backward_impl(const GradSmallParams& gp, int b, cudaStream_t st) {
-  const size_t smem = (size_t)3 * (gp.cnt[0] + gp.cnt[1]) * sizeof(float);
-  const int rc = gp.cnt[0] + gp.cnt[1] >= 2048 ? launch_grad_small_t<1024>(gp, b, smem, st)
-                                               : launch_grad_small_t<256>(gp, b, smem, st);
+int small_backward_impl(GradSmallParams gp, int b, cudaStream_t st) {
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  gp.parts = grad_small_parts(b, gp.cnt[0], gp.cnt[1], di.sms);
+  const int own = (gp.cnt[0] + gp.parts - 1) / gp.parts + (gp.cnt[1] + gp.parts - 1) / gp.parts;  // rows a CTA owns
+  const size_t smem = (size_t)3 * own * sizeof(float);
+  const long long grid = (long long)b * gp.parts;
+  if (grid > 0x7fffffffLL || smem > 220 * 1024) return NND_EINVAL;
+  rc = own >= 2048 ? launch_grad_small_t<1024>(gp, grid, smem, st) : launch_grad_small_t<256>(gp, grid, smem, st);
   if (rc) return rc;
   ++g_launches;
   debug_sync("small_backward", st);
@@ -1263,7 +1285,7 @@ const char* nnd_error_string(int code) {
 
 size_t nnd_workspace_bytes(int b, int n, int m) {
   if (b <= 0 || n <= 0 || m <= 0) return 256;
-  if (use_small(n, m)) return 0;  // single-launch path: no workspace (the pointer may be null)
+  if (use_small(b, n, m)) return 0;  // single-launch path: no workspace (the pointer may be null)
   return nnd_rows_workspace_bytes(b, n, m) + colkey_bytes(b, m);
 }
 
@@ -1279,9 +1301,9 @@ size_t nnd_colkeys_count(int b, int m) {
 
 int nnd_row_group(void) { return kRowAlign; }
 
-int nnd_forward_is_symmetric(int n, int m) { return !use_small(n, m) && use_symmetric(n, m) ? 1 : 0; }
+int nnd_forward_is_symmetric(int n, int m) { return !use_small(1 << 20, n, m) && use_symmetric(n, m) ? 1 : 0; }
 
-int nnd_forward_kind(int n, int m) { return use_small(n, m) ? 0 : use_symmetric(n, m) ? 2 : 1; }
+int nnd_forward_kind(int b, int n, int m) { return use_small(b, n, m) ? 0 : use_symmetric(n, m) ? 2 : 1; }
 
 int nnd_small_max_points(void) { return small_max_points(); }
 
@@ -1316,7 +1338,7 @@ int nnd_set_sym_seed_tiles(int tiles) {
 
 size_t nnd_query_workspace_bytes(int b, int nq, int nt) {
   if (b <= 0 || nq <= 0 || nt <= 0) return 256;
-  if (use_small(nq, nt)) return 0;
+  if (use_small(b, nq, nt)) return 0;
   return soa_bytes(b, nq) + soa_bytes(b, nt) + key_bytes(b, nq);
 }
 
@@ -1336,7 +1358,7 @@ int nnd_forward_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int
   if (n == 0) return zero_outputs(dist2, idx2, (long long)b * m, st);  // my_lib.cpp:9-10,21-22 with an empty inner loop
   if (m == 0) return zero_outputs(dist1, idx1, (long long)b * n, st);
   if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2) return NND_EINVAL;
-  if (use_small(n, m))
+  if (use_small(b, n, m))
     return small_forward_impl(xyz1, n, xyz2, m, b, 2, nullptr, nullptr, dist1, idx1, dist2, idx2, st);
   if (!workspace) return NND_EINVAL;
   if (workspace_bytes < nnd_workspace_bytes(b, n, m)) return NND_EWORKSPACE;
@@ -1409,7 +1431,7 @@ int nnd_query_cuda_f32(const float* query, const float* target, int b, int nq, i
   if (b == 0 || nq == 0) return 0;
   if (nt == 0) return zero_outputs(dist, idx, (long long)b * nq, st);
   if (!query || !target || !dist || !idx) return NND_EINVAL;
-  if (use_small(nq, nt))
+  if (use_small(b, nq, nt))
     return small_forward_impl(query, nq, target, nt, b, 1, nullptr, nullptr, dist, idx, nullptr, nullptr, st);
   if (!workspace) return NND_EINVAL;
   return twopass_impl(query, nq, target, nt, b, 1, dist, idx, nullptr, nullptr, workspace, workspace_bytes, st);
@@ -1499,10 +1521,10 @@ int nnd_backward_cuda_f32(const float* xyz1, const float* xyz2, const float* gra
   cudaStream_t st = (cudaStream_t)stream;
   if (b == 0) return 0;
   if ((n > 0 && !gradxyz1) || (m > 0 && !gradxyz2)) return NND_EINVAL;
-  if (n > 0 && m > 0 && use_small_grad(n, m)) {  // one launch: zero-init, both terms and the stores
+  if (n > 0 && m > 0 && use_small(b, n, m)) {  // one launch: zero-init, both terms and the stores
     if (!xyz1 || !xyz2 || !graddist1 || !graddist2 || !idx1 || !idx2) return NND_EINVAL;
     GradSmallParams sp{{xyz1, xyz2}, {graddist1, graddist2}, {idx1, idx2}, {gradxyz1, gradxyz2}, {nullptr, nullptr},
-                       {n, m}, 2};
+                       {n, m}, 2, 1};
     return small_backward_impl(sp, b, st);
   }
   cudaError_t e = cudaSuccess;  // zero-init fused into the call (my_lib.cpp:91-94)
@@ -1519,7 +1541,7 @@ int nnd_backward_cuda_f32(const float* xyz1, const float* xyz2, const float* gra
 }
 
 // ---- ragged batches (per-cloud lengths), single-launch kernels only
-int nnd_ragged_supported(int n, int m) { return use_small_grad(n, m) ? 1 : 0; }
+int nnd_ragged_supported(int n, int m) { return use_small_nm(n, m) ? 1 : 0; }
 
 int nnd_forward_ragged_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int m, const long long* len1,
                                 const long long* len2, float* dist1, float* dist2, int32_t* idx1, int32_t* idx2,
@@ -1530,7 +1552,7 @@ int nnd_forward_ragged_cuda_f32(const float* xyz1, const float* xyz2, int b, int
   if (b == 0 || (n == 0 && m == 0)) return 0;
   if (n == 0) return zero_outputs(dist2, idx2, (long long)b * m, st);
   if (m == 0) return zero_outputs(dist1, idx1, (long long)b * n, st);
-  if (!use_small_grad(n, m)) return NND_EINVAL;
+  if (!use_small_nm(n, m)) return NND_EINVAL;
   if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2) return NND_EINVAL;
   return small_forward_impl(xyz1, n, xyz2, m, b, 2, len1, len2, dist1, idx1, dist2, idx2, st);
 }
@@ -1542,7 +1564,7 @@ int nnd_query_ragged_cuda_f32(const float* query, const float* target, int b, in
   cudaStream_t st = (cudaStream_t)stream;
   if (b == 0 || nq == 0) return 0;
   if (nt == 0) return zero_outputs(dist, idx, (long long)b * nq, st);
-  if (!use_small_grad(nq, nt)) return NND_EINVAL;
+  if (!use_small_nm(nq, nt)) return NND_EINVAL;
   if (!query || !target || !dist || !idx) return NND_EINVAL;
   return small_forward_impl(query, nq, target, nt, b, 1, lenq, lent, dist, idx, nullptr, nullptr, st);
 }
@@ -1553,9 +1575,9 @@ int nnd_backward_ragged_cuda_f32(const float* xyz1, const float* xyz2, const flo
   g_launches = 0;
   if (b < 0 || n <= 0 || m <= 0) return NND_EINVAL;
   if (b == 0) return 0;
-  if (!use_small_grad(n, m)) return NND_EINVAL;
+  if (!use_small_nm(n, m)) return NND_EINVAL;
   if (!xyz1 || !xyz2 || !graddist1 || !graddist2 || !idx1 || !idx2 || !gradxyz1 || !gradxyz2) return NND_EINVAL;
-  GradSmallParams sp{{xyz1, xyz2}, {graddist1, graddist2}, {idx1, idx2}, {gradxyz1, gradxyz2}, {len1, len2}, {n, m}, 2};
+  GradSmallParams sp{{xyz1, xyz2}, {graddist1, graddist2}, {idx1, idx2}, {gradxyz1, gradxyz2}, {len1, len2}, {n, m}, 2, 1};
   return small_backward_impl(sp, b, (cudaStream_t)stream);
 }
 
@@ -1565,10 +1587,10 @@ int nnd_knn_backward_ragged_cuda_f32(const float* query, const float* target, co
   g_launches = 0;
   if (b < 0 || nq <= 0 || nt <= 0) return NND_EINVAL;
   if (b == 0) return 0;
-  if (!use_small_grad(nq, nt)) return NND_EINVAL;
+  if (!use_small_nm(nq, nt)) return NND_EINVAL;
   if (!query || !target || !graddist || !idx || !grad_query || !grad_target) return NND_EINVAL;
   GradSmallParams sp{{query, target}, {graddist, nullptr}, {idx, nullptr}, {grad_query, grad_target}, {lenq, lent},
-                     {nq, nt}, 1};
+                     {nq, nt}, 1, 1};
   return small_backward_impl(sp, b, (cudaStream_t)stream);
 }
 

@@ -19,9 +19,10 @@
 //    in the same grid.  Optional per-cloud lengths (ragged batches, loss.py:143-144): rows past the length get
 //    dist = 0, idx = 0, neighbours are searched among the first len points only.
 //
-//  nnd_grad_small_kernel: one CTA = one batch element.  Both gradients of the element are accumulated in shared
-//    memory (own-row terms by plain stores, which doubles as the zero-init; neighbour-row terms by shared-memory
-//    atomics: no global memset, no global atomics) and written out once with plain coalesced stores.
+//  nnd_grad_small_kernel: every CTA owns a range of rows of both gradients of one batch element and accumulates
+//    them in shared memory (own-row terms by plain stores, which doubles as the zero-init; neighbour-row terms by
+//    shared-memory atomics after reading the whole neighbour-index arrays: no global memset, no global atomics) and
+//    writes them out once with plain coalesced stores.
 
 constexpr int kSmallChunk = 16;  // targets per lazy-index chunk (the re-scan that resolves the index costs one chunk)
 
@@ -195,7 +196,16 @@ __global__ void __launch_bounds__(WARPS * 32) nnd_small_kernel(const __grid_cons
 
 // ----------------------------------------------------------------------------------------------------------------
 // Backward for small clouds (my_lib.cpp:91-130 / nnd_cuda.cu:164-183): t_c = fl(fl(2 g) * fl(q_c - target_c)),
-// own row += t, neighbour row -= t.  One CTA per batch element; accumulators in shared memory.
+// own row += t, neighbour row -= t.
+// One batch element is cut into `parts` CTAs; CTA (batch, part) OWNS the rows [c*part/parts, c*(part+1)/parts) of both
+// gradients and keeps them in shared memory:
+//   phase 0: the own-row terms of its rows, plain stores (every owned entry is written exactly once: this is also the
+//            zero-init; rows at or past the cloud's length get 0);
+//   phase 1: it reads the WHOLE neighbour-index array of both terms (coalesced, 4 B per row) and, for the rows whose
+//            neighbour lies in its range, recomputes the term and subtracts it with a shared-memory atomic
+//            (fp32 atomicAdd on shared memory is a compare-and-swap loop on this part: SASS ATOMS.CAST.SPIN);
+//   then it writes its rows out with plain coalesced stores.
+// No global memset, no global atomics, one launch; `parts` > 1 only spreads a small batch over more SMs.
 struct GradSmallParams {
   const float* xyz[2];      // [b][cnt[s]][3]
   const float* gd[2];       // [b][cnt[s]]   upstream gradient of dist_s
@@ -204,41 +214,44 @@ struct GradSmallParams {
   const long long* len[2];  // optional valid lengths
   int cnt[2];
   int nterms;  // 2: both terms (nnd backward).  1: term 0 only (one-direction knn backward); grad[1] still overwritten
+  int parts;   // CTAs per batch element
 };
 
-// One term of one batch element: rows r of cloud s with neighbours j = ix[r] in the other cloud.
-// phase 0: own-row terms, plain stores (every accumulator entry of cloud s is written exactly once here: this is also
-//          the zero-init, rows at or past the length get 0);  phase 1: neighbour-row terms, shared-memory atomics
-//          (fp32 atomicAdd on shared memory is a compare-and-swap loop on this part: SASS ATOMS.CAST.SPIN).
-template <int THREADS, int PHASE>
-__device__ __forceinline__ void grad_small_term(const float* __restrict__ q, const float* __restrict__ t,
-                                                const float* __restrict__ gd, const int32_t* __restrict__ ix,
-                                                float* aq, float* at, int live, int cnt, bool has_term) {
-  const int tid = threadIdx.x;
-  if (PHASE == 0) {
-    for (int r = tid; r < cnt; r += THREADS) {
-      float tx = 0.f, ty = 0.f, tz = 0.f;
-      if (has_term && r < live) {
-        const int j = __ldg(ix + r);
-        const float g = __fmul_rn(__ldg(gd + r), 2.0f);
-        tx = __fmul_rn(g, __fsub_rn(__ldg(q + 3 * r), __ldg(t + 3 * j)));
-        ty = __fmul_rn(g, __fsub_rn(__ldg(q + 3 * r + 1), __ldg(t + 3 * j + 1)));
-        tz = __fmul_rn(g, __fsub_rn(__ldg(q + 3 * r + 2), __ldg(t + 3 * j + 2)));
-      }
-      aq[3 * r] = tx;
-      aq[3 * r + 1] = ty;
-      aq[3 * r + 2] = tz;
-    }
-  } else if (has_term) {
-    for (int r = tid; r < live; r += THREADS) {
+__device__ __forceinline__ void grad_small_own(const float* __restrict__ q, const float* __restrict__ t,
+                                               const float* __restrict__ gd, const int32_t* __restrict__ ix, float* acc,
+                                               int lo, int hi, int live, bool has_term, int tid, int threads) {
+  for (int r = lo + tid; r < hi; r += threads) {
+    float tx = 0.f, ty = 0.f, tz = 0.f;
+    if (has_term && r < live) {
       const int j = __ldg(ix + r);
+      const float g = __fmul_rn(__ldg(gd + r), 2.0f);
+      tx = __fmul_rn(g, __fsub_rn(__ldg(q + 3 * r), __ldg(t + 3 * j)));
+      ty = __fmul_rn(g, __fsub_rn(__ldg(q + 3 * r + 1), __ldg(t + 3 * j + 1)));
+      tz = __fmul_rn(g, __fsub_rn(__ldg(q + 3 * r + 2), __ldg(t + 3 * j + 2)));
+    }
+    float* a = acc + 3 * (r - lo);
+    a[0] = tx;
+    a[1] = ty;
+    a[2] = tz;
+  }
+}
+
+// rows r of cloud s (all of them) whose neighbour j = ix[r] lies in [lo, hi) of the other cloud: acc[j - lo] -= t
+__device__ __forceinline__ void grad_small_scatter(const float* __restrict__ q, const float* __restrict__ t,
+                                                   const float* __restrict__ gd, const int32_t* __restrict__ ix,
+                                                   float* acc, int lo, int hi, int live, int tid, int threads) {
+#pragma unroll 4
+  for (int r = tid; r < live; r += threads) {
+    const int j = __ldg(ix + r);
+    if (j >= lo && j < hi) {
       const float g = __fmul_rn(__ldg(gd + r), 2.0f);
       const float tx = __fmul_rn(g, __fsub_rn(__ldg(q + 3 * r), __ldg(t + 3 * j)));
       const float ty = __fmul_rn(g, __fsub_rn(__ldg(q + 3 * r + 1), __ldg(t + 3 * j + 1)));
       const float tz = __fmul_rn(g, __fsub_rn(__ldg(q + 3 * r + 2), __ldg(t + 3 * j + 2)));
-      atomicAdd(at + 3 * j, -tx);
-      atomicAdd(at + 3 * j + 1, -ty);
-      atomicAdd(at + 3 * j + 2, -tz);
+      float* a = acc + 3 * (j - lo);
+      atomicAdd(a, -tx);
+      atomicAdd(a + 1, -ty);
+      atomicAdd(a + 2, -tz);
     }
   }
 }
@@ -246,10 +259,13 @@ __device__ __forceinline__ void grad_small_term(const float* __restrict__ q, con
 template <int THREADS>
 __global__ void __launch_bounds__(THREADS) nnd_grad_small_kernel(const __grid_constant__ GradSmallParams p) {
   extern __shared__ __align__(16) float gsmall_acc[];
-  const int batch = blockIdx.x, tid = threadIdx.x;
+  const int tid = threadIdx.x;
+  const int batch = blockIdx.x / p.parts, part = blockIdx.x - batch * p.parts;
   const int c0 = p.cnt[0], c1 = p.cnt[1];
+  const int lo0 = (int)((long long)c0 * part / p.parts), hi0 = (int)((long long)c0 * (part + 1) / p.parts);
+  const int lo1 = (int)((long long)c1 * part / p.parts), hi1 = (int)((long long)c1 * (part + 1) / p.parts);
   float* acc0 = gsmall_acc;
-  float* acc1 = gsmall_acc + 3 * c0;
+  float* acc1 = gsmall_acc + 3 * (hi0 - lo0);
   int l0 = c0, l1 = c1;
   if (p.len[0] != nullptr) l0 = clamp_len(p.len[0][batch], c0);
   if (p.len[1] != nullptr) l1 = clamp_len(p.len[1][batch], c1);
@@ -261,14 +277,14 @@ __global__ void __launch_bounds__(THREADS) nnd_grad_small_kernel(const __grid_co
   const bool two = p.nterms == 2;
   const float* gd1 = two ? p.gd[1] + (long long)batch * c1 : nullptr;
   const int32_t* ix1 = two ? p.idx[1] + (long long)batch * c1 : nullptr;
-  grad_small_term<THREADS, 0>(x0, x1, gd0, ix0, acc0, acc1, l0, c0, true);
-  grad_small_term<THREADS, 0>(x1, x0, gd1, ix1, acc1, acc0, l1, c1, two);
+  grad_small_own(x0, x1, gd0, ix0, acc0, lo0, hi0, l0, true, tid, THREADS);
+  grad_small_own(x1, x0, gd1, ix1, acc1, lo1, hi1, l1, two, tid, THREADS);
   __syncthreads();
-  grad_small_term<THREADS, 1>(x0, x1, gd0, ix0, acc0, acc1, l0, c0, true);
-  grad_small_term<THREADS, 1>(x1, x0, gd1, ix1, acc1, acc0, l1, c1, two);
+  grad_small_scatter(x0, x1, gd0, ix0, acc1, lo1, hi1, l0, tid, THREADS);          // term 1 lands in cloud 2's rows
+  if (two) grad_small_scatter(x1, x0, gd1, ix1, acc0, lo0, hi0, l1, tid, THREADS);  // term 2 lands in cloud 1's rows
   __syncthreads();
-  float* g0 = p.grad[0] + (long long)batch * c0 * 3;
-  float* g1 = p.grad[1] + (long long)batch * c1 * 3;
-  for (int i = tid; i < 3 * c0; i += THREADS) g0[i] = acc0[i];
-  for (int i = tid; i < 3 * c1; i += THREADS) g1[i] = acc1[i];
+  float* g0 = p.grad[0] + ((long long)batch * c0 + lo0) * 3;
+  float* g1 = p.grad[1] + ((long long)batch * c1 + lo1) * 3;
+  for (int i = tid; i < 3 * (hi0 - lo0); i += THREADS) g0[i] = acc0[i];
+  for (int i = tid; i < 3 * (hi1 - lo1); i += THREADS) g1[i] = acc1[i];
 }

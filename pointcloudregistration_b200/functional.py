@@ -34,7 +34,8 @@ def _check_clouds(xyz1: torch.Tensor, xyz2: torch.Tensor) -> None:
 
 
 def _stream_ptr(device: torch.device) -> int:
-    return torch.cuda.current_stream(device).cuda_stream
+    # the raw cudaStream_t of torch's current stream; ~10x cheaper than building a torch.cuda.Stream object
+    return torch._C._cuda_getCurrentRawStream(device.index if device.index is not None else torch.cuda.current_device())
 
 
 def _workspace(nbytes: int, device: torch.device) -> torch.Tensor:

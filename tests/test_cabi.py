@@ -51,11 +51,14 @@ def test_workspace_size_formula(cuda_lib):
     # small clouds take the single-launch kernels: no workspace at all
     assert cuda_lib.nnd_small_max_points() == 4096
     assert cuda_lib.nnd_workspace_bytes(256, 256, 256) == 0 and cuda_lib.nnd_query_workspace_bytes(2, 512, 512) == 0
-    assert cuda_lib.nnd_forward_kind(256, 256) == 0 and cuda_lib.nnd_forward_kind(4096, 4097) == 1
-    assert cuda_lib.nnd_forward_kind(16384, 16384) == 2 and cuda_lib.nnd_ragged_supported(3000, 2900) == 1
+    assert cuda_lib.nnd_forward_kind(256, 256, 256) == 0 and cuda_lib.nnd_forward_kind(4, 4096, 4097) == 1
+    assert cuda_lib.nnd_forward_kind(32, 16384, 16384) == 2 and cuda_lib.nnd_ragged_supported(3000, 2900) == 1
+    # a lone pair keeps the single launch up to ~10 k points (the general path cannot fill the machine there)
+    assert cuda_lib.nnd_forward_kind(1, 8192, 8192) == 0 and cuda_lib.nnd_forward_kind(1, 10241, 100) == 1
+    assert cuda_lib.nnd_forward_kind(2, 8192, 8192) == 2 and cuda_lib.nnd_workspace_bytes(1, 9000, 9000) == 0
     before = cuda_lib.nnd_set_small_max_points(0)
     try:
-        assert cuda_lib.nnd_workspace_bytes(1, 256, 256) > 0 and cuda_lib.nnd_forward_kind(256, 256) == 1
+        assert cuda_lib.nnd_workspace_bytes(1, 256, 256) > 0 and cuda_lib.nnd_forward_kind(1, 256, 256) == 1
     finally:
         cuda_lib.nnd_set_small_max_points(before)
     assert cuda_lib.nnd_set_small_config(8, 3, 1) == 10001 and cuda_lib.nnd_set_small_config(8, 2, 3) == 10001
