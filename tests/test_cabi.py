@@ -47,7 +47,7 @@ def test_workspace_size_formula(cuda_lib):
     # the row-range entry point keeps the column keys in a caller-owned buffer (they are all-reduced)
     assert cuda_lib.nnd_rows_workspace_bytes(1, 1_000_000, 1_000_000) + 8 * cuda_lib.nnd_colkeys_count(1, 1_000_000) <= w
     assert cuda_lib.nnd_colkeys_count(3, 513) == 3 * 1024 and cuda_lib.nnd_row_group() == 8
-    assert cuda_lib.nnd_query_workspace_bytes(2, 5120, 5120) == 2 * (2 * 5120 * 12) + 2 * 5120 * 8
+    assert cuda_lib.nnd_query_workspace_bytes(4, 5120, 5120) == 2 * (4 * 5120 * 12) + 4 * 5120 * 8
     # small clouds take the single-launch kernels: no workspace at all
     assert cuda_lib.nnd_small_max_points() == 4096
     assert cuda_lib.nnd_workspace_bytes(256, 256, 256) == 0 and cuda_lib.nnd_query_workspace_bytes(2, 512, 512) == 0
