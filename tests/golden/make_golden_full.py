@@ -35,6 +35,8 @@ OUT = HERE / "digests_full.json"
 
 # name -> (kind, b, n, m, config number = seeds)
 CASES = {
+    "c1_uniform": ("uniform", 1, 2048, 2048, 1),
+    "dip_uniform": ("uniform", 256, 256, 256, 6),  # the shape DIP really trains on (dip/train.py:84)
     "c2_uniform": ("uniform", 32, 16384, 16384, 2),
     "c3_uniform": ("uniform", 1, 100_000, 100_000, 3),
     "c5_lattice": ("lattice", 1, 262_144, 262_144, 5),
