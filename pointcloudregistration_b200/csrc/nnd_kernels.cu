@@ -1117,9 +1117,10 @@ inline bool use_small(int b, int n, int m) {
 }
 // Ragged batches and the one-launch backward key on the cloud sizes alone (no batch term): <= small_max_points().
 inline bool use_small_nm(int n, int m) { return (n > m ? n : m) <= small_max_points(); }
-// CTAs per batch element of the shared-memory backward: enough to put ~2 CTAs on every SM when the batch is small.
+// CTAs per batch element of the shared-memory backward: one when the batch alone fills the machine (every extra part
+// re-reads the whole index arrays), up to 16 for a lone pair.
 inline int grad_small_parts(int b, int n, int m, int sms) {
-  long long parts = (2ll * sms + b - 1) / b;
+  long long parts = sms / (b > 0 ? b : 1);
   const long long by_rows = ((long long)n + m) / 256;  // at least ~256 owned rows per CTA
   if (parts > by_rows) parts = by_rows;
   if (parts > 16) parts = 16;
@@ -1234,7 +1235,12 @@ int small_backward_impl(GradSmallParams gp, int b, cudaStream_t st) {
   const size_t smem = (size_t)3 * own * sizeof(float);
   const long long grid = (long long)b * gp.parts;
   if (grid > 0x7fffffffLL || smem > 220 * 1024) return NND_EINVAL;
-  rc = own >= 2048 ? launch_grad_small_t<1024>(gp, grid, smem, st) : launch_grad_small_t<256>(gp, grid, smem, st);
+  // every CTA walks ALL rows of both clouds in phase 1 (dependent gathers behind each index): enough threads that a
+  // thread sees at most ~4 rows, so its loads are one batch in flight instead of a chain of batches
+  const long long scan = (long long)gp.cnt[0] + gp.cnt[1];
+  rc = scan > 2048 ? launch_grad_small_t<1024>(gp, grid, smem, st)
+     : scan > 1024 ? launch_grad_small_t<512>(gp, grid, smem, st)
+                   : launch_grad_small_t<256>(gp, grid, smem, st);
   if (rc) return rc;
   ++g_launches;
   debug_sync("small_backward", st);

@@ -257,7 +257,7 @@ __device__ __forceinline__ void grad_small_scatter(const float* __restrict__ q, 
 }
 
 template <int THREADS>
-__global__ void __launch_bounds__(THREADS) nnd_grad_small_kernel(const __grid_constant__ GradSmallParams p) {
+__global__ void __launch_bounds__(THREADS, 1) nnd_grad_small_kernel(const __grid_constant__ GradSmallParams p) {
   extern __shared__ __align__(16) float gsmall_acc[];
   const int tid = threadIdx.x;
   const int batch = blockIdx.x / p.parts, part = blockIdx.x - batch * p.parts;

@@ -493,8 +493,10 @@ def test_aten_shim_writes_in_place(cuda_lib, device):
 def panels_forced(cuda_lib):
     """Push every symmetric scan through nnd_scan_symc_kernel (normally only row ranges >= 200 000 rows)."""
     before = cuda_lib.nnd_set_panel_min_rows(1)
+    small = cuda_lib.nnd_set_small_max_points(0)  # a lone pair of <= 10 k points would take the single-launch kernel
     yield
     cuda_lib.nnd_set_panel_min_rows(before)
+    cuda_lib.nnd_set_small_max_points(small)
 
 
 @pytest.mark.parametrize("kind,b,n,m", [
