@@ -407,7 +407,7 @@ class Runner:
 
     def scan_kernel(self):
         """(name, distance evaluations one rank's scan executes per step)"""
-        from pointcloudregistration_b200.sharded import shard_range
+        from pointcloudregistration_b200.sharded import uniform_shard_range
 
         lib, b, n, m, world = self.lib, self.b, self.n, self.m, self.world
         if world == 1:
@@ -416,7 +416,7 @@ class Runner:
                 return SCAN_NAMES[kind], self.pairs
             lo, hi = 0, n
         else:
-            lo, hi = shard_range(n, world, 0, align=lib.nnd_row_group())
+            lo, hi = uniform_shard_range(n, world, 0, align=lib.nnd_row_group())
         rk = lib.nnd_rows_scan_kind(b, n, m, lo, hi)
         return SCAN_NAMES[{1: "sym", 2: "panel", 3: "swapped"}.get(rk, "sym")], self.pairs / 2 / world
 

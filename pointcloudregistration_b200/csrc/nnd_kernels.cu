@@ -1383,7 +1383,8 @@ int nnd_forward_rows_cuda_f32(const float* xyz1, const float* xyz2, int b, int n
   g_launches = 0;
   if (!sizes_ok(b, n, m) || b == 0 || n == 0 || m == 0) return NND_EINVAL;
   if (row_lo < 0 || row_hi < row_lo || row_hi > n) return NND_EINVAL;
-  if (row_lo % kRowAlign != 0 || (row_hi % kRowAlign != 0 && row_hi != n)) return NND_EINVAL;  // whole row groups
+  // whole row groups; an empty range at the very end (a rank left without rows) is fine
+  if ((row_lo % kRowAlign != 0 && row_lo != n) || (row_hi % kRowAlign != 0 && row_hi != n)) return NND_EINVAL;
   if (!xyz1 || !xyz2 || !dist1 || !idx1 || !colkeys || !workspace) return NND_EINVAL;
   return forward_rows_impl(xyz1, n, xyz2, m, b, row_lo, row_hi, dist1, idx1, colkeys, workspace, workspace_bytes,
                            (cudaStream_t)stream);

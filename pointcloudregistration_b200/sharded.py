@@ -38,6 +38,18 @@ import torch.distributed as dist
 from torch.autograd import Function
 
 
+#: set to a list to get a timeline of one step: _mark() then appends (phase name, CUDA event recorded on the current stream
+#: once that phase's work has been enqueued / waited for); tools/sharded_timeline.py turns it into per-phase milliseconds
+trace = None
+
+
+def _mark(name: str, ref: torch.Tensor) -> None:
+    if trace is not None and ref.is_cuda:
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record(torch.cuda.current_stream(ref.device))
+        trace.append((name, ev))
+
+
 def shard_range(n: int, world: int, rank: int, align: int = 1) -> tuple[int, int]:
     """Contiguous balanced split of n rows; interior boundaries are rounded down to multiples of `align`."""
     def cut(r: int) -> int:
@@ -46,6 +58,20 @@ def shard_range(n: int, world: int, rank: int, align: int = 1) -> tuple[int, int
         return (n * r) // world // align * align
 
     return cut(rank), cut(rank + 1)
+
+
+def uniform_shard_range(n: int, world: int, rank: int, align: int = 1) -> tuple[int, int]:
+    """Rows [rank * rpr, min(n, (rank + 1) * rpr)) with one stride rpr = ceil(n / world) rounded up to `align` for every
+    rank: the row shards of cloud 1.  With a common stride the all_gather of the shards IS the full array (rank-major
+    concatenation, cut at n): no per-rank offsets, no re-packing.  The last ranks may get fewer rows (or none, for tiny
+    clouds); at 1M rows and 8 ranks every shard is exactly 125 000 rows."""
+    rpr = shard_stride(n, world, align)
+    lo = min(n, rank * rpr)
+    return lo, min(n, lo + rpr)
+
+
+def shard_stride(n: int, world: int, align: int = 1) -> int:
+    return max(align, -(-(-(-n // world)) // align) * align)  # ceil(ceil(n / world) / align) * align, at least align
 
 
 @dataclass
@@ -132,7 +158,8 @@ def _world(group):
 
 
 def _gather_rows(shard: torch.Tensor, n: int, world: int, group, align: int) -> torch.Tensor:
-    """all_gather of [B, rows_r] shards (rows_r = shard_range sizes) -> [B, n]."""
+    """all_gather of [B, rows_r] shards (rows_r = shard_range sizes) -> [B, n].  General form (any split): used for the
+    cloud-2 slices of the deterministic backward's inputs."""
     if world == 1:
         return shard.contiguous()
     b = shard.size(0)
@@ -145,17 +172,46 @@ def _gather_rows(shard: torch.Tensor, n: int, world: int, group, align: int) -> 
     return torch.cat([bufs[r][:, :hi - lo] for r, (lo, hi) in enumerate(ranges)], dim=1)
 
 
+def _gather_pair_start(a: torch.Tensor, c: torch.Tensor, n: int, world: int, group, align: int):
+    """Starts ONE all_gather for two [B, rows] 4-byte shards of cloud-1 rows (uniform_shard_range: common stride).
+    Send layout [2, B, stride], receive layout [world, 2, B, stride]; returns (work handle, receive buffer).
+    Two small copies in, nothing zero-filled (the padding is never read)."""
+    b, rows = a.shape
+    stride = shard_stride(n, world, align)
+    send = torch.empty(2, b, stride, dtype=torch.int32, device=a.device)
+    send[0, :, :rows] = a.view(torch.int32)
+    send[1, :, :rows] = c.view(torch.int32)
+    recv = torch.empty(world * 2, b, stride, dtype=torch.int32, device=a.device)  # concatenation along dim 0 (the
+    work = dist.all_gather_into_tensor(recv, send, group=group, async_op=True)    # form every backend accepts)
+    return work, recv.view(world, 2, b, stride)
+
+
+def _gather_pair_finish(work, recv: torch.Tensor, n: int, dtype_a, dtype_c):
+    """Waits for the gather and returns the two full [B, n] tensors (own storage each: one strided copy per tensor)."""
+    work.wait()
+    world, _, b, stride = recv.shape
+    out = []
+    for which, dtype in ((0, dtype_a), (1, dtype_c)):
+        # [world, B, stride] -> [B, world * stride]: rank-major rows; the chunks of one tensor are 2*B*stride apart in
+        # recv, so this reshape is always a copy into storage of its own
+        full = recv[:, which].permute(1, 0, 2).reshape(b, world * stride)
+        out.append(full[:, :n].contiguous().view(dtype))  # no-op for one cloud pair (a [1, n] prefix is contiguous)
+    return out[0], out[1]
+
+
 def sharded_forward(xyz1, xyz2, group=None, src=None, gather=True, compute=CudaCompute):
     """Returns (dist1, dist2, idx1, idx2, info).  With gather=True the four tensors are full-size and
     identical on every rank; otherwise they are this rank's row shards ([lo1,hi1) of cloud 1, [lo2,hi2) of
     cloud 2)."""
     rank, world = _world(group)
+    _mark("start", xyz1)
     if src is not None and world > 1:
         dist.broadcast(xyz1, src=src, group=group)
         dist.broadcast(xyz2, src=src, group=group)
+        _mark("broadcast xyz1, xyz2", xyz1)
     n, m = xyz1.size(1), xyz2.size(1)
     align = compute.row_group()
-    lo1, hi1 = shard_range(n, world, rank, align)
+    lo1, hi1 = uniform_shard_range(n, world, rank, align)
     lo2, hi2 = shard_range(m, world, rank)
     info = ShardInfo(rank, world, lo1, hi1, lo2, hi2)
     if xyz1.size(0) == 0 or n == 0 or m == 0:  # my_lib.cpp:9-10,21-22: empty inner loop -> zeros
@@ -164,15 +220,21 @@ def sharded_forward(xyz1, xyz2, group=None, src=None, gather=True, compute=CudaC
         (d1, i1), (d2, i2) = z(n if gather else hi1 - lo1), z(m if gather else hi2 - lo2)
         return d1, d2, i1, i2, info
     d1, i1, colkeys = compute.rows(xyz1, xyz2, lo1, hi1)
+    _mark("rows kernel (prepare + scan + finalize rows)", xyz1)
+    pending = None
     if world > 1:
-        dist.all_reduce(colkeys, op=dist.ReduceOp.MIN, group=group)
+        # the one real exchange step first (the column finalize waits for it) ...
+        kwork = dist.all_reduce(colkeys, op=dist.ReduceOp.MIN, group=group, async_op=True)
+        if gather:  # ... then the row results: one collective, in flight while the column finalize runs
+            pending = _gather_pair_start(d1.contiguous(), i1.contiguous(), n, world, group, align)
+        kwork.wait()
+        _mark("all_reduce(MIN) column keys", xyz1)
     d2, i2 = compute.finalize_cols(xyz1, xyz2, colkeys)
+    _mark("finalize columns", xyz1)
     if gather:
-        if world > 1:  # one collective for both row results: dist bits and idx travel as int32 side by side
-            both = _gather_rows(torch.cat([d1.contiguous().view(torch.int32), i1.contiguous()], dim=0), n, world,
-                                group, align)
-            b = xyz1.size(0)
-            d1, i1 = both[:b].clone().view(torch.float32), both[b:].clone()  # own storage each (dtype differs)
+        if pending is not None:
+            d1, i1 = _gather_pair_finish(*pending, n, torch.float32, torch.int32)
+            _mark("all_gather dist1/idx1 (issued before the column finalize) + unpack", xyz1)
         else:
             d1, i1 = d1.contiguous(), i1.contiguous()
     else:
@@ -193,11 +255,11 @@ def sharded_backward(xyz1, xyz2, graddist1, graddist2, idx1, idx2, info: ShardIn
     if exact:
         if not gathered and info.world > 1:  # shards in: one all_gather per cloud (bits side by side, like the forward)
             n, m, b = xyz1.size(1), xyz2.size(1), xyz1.size(0)
-            both1 = _gather_rows(torch.cat([graddist1.contiguous().view(torch.int32), idx1.contiguous()], dim=0), n,
-                                 info.world, group, compute.row_group())
+            pending = _gather_pair_start(graddist1.contiguous(), idx1.contiguous(), n, info.world, group,
+                                         compute.row_group())
             both2 = _gather_rows(torch.cat([graddist2.contiguous().view(torch.int32), idx2.contiguous()], dim=0), m,
                                  info.world, group, 1)
-            graddist1, idx1 = both1[:b].clone().view(torch.float32), both1[b:].clone()
+            graddist1, idx1 = _gather_pair_finish(*pending, n, torch.float32, torch.int32)
             graddist2, idx2 = both2[:b].clone().view(torch.float32), both2[b:].clone()
         return compute.backward_exact(xyz1, xyz2, graddist1.contiguous(), graddist2.contiguous(), idx1.contiguous(),
                                       idx2.contiguous())
@@ -208,14 +270,22 @@ def sharded_backward(xyz1, xyz2, graddist1, graddist2, idx1, idx2, info: ShardIn
     flat = torch.zeros(xyz1.numel() + xyz2.numel(), dtype=xyz1.dtype, device=xyz1.device)
     g1 = flat[:xyz1.numel()].view_as(xyz1)
     g2 = flat[xyz1.numel():].view_as(xyz2)
-    own1 = torch.zeros(xyz1.size(0), hi1 - lo1, 3, dtype=xyz1.dtype, device=xyz1.device)
-    own2 = torch.zeros(xyz2.size(0), hi2 - lo2, 3, dtype=xyz2.dtype, device=xyz2.device)
-    compute.backward_term(xyz1[:, lo1:hi1].contiguous(), xyz2, graddist1.contiguous(), idx1.contiguous(), own1, g2)
-    compute.backward_term(xyz2[:, lo2:hi2].contiguous(), xyz1, graddist2.contiguous(), idx2.contiguous(), own2, g1)
-    g1[:, lo1:hi1] += own1
-    g2[:, lo2:hi2] += own2
+    if xyz1.size(0) == 1:
+        # one cloud pair (the large-cloud case): a row range of a [1, n, 3] tensor is contiguous, so the own-row terms
+        # accumulate straight into the flat buffer -- no shard buffers, no copies, no extra adds
+        compute.backward_term(xyz1[:, lo1:hi1], xyz2, graddist1.contiguous(), idx1.contiguous(), g1[:, lo1:hi1], g2)
+        compute.backward_term(xyz2[:, lo2:hi2], xyz1, graddist2.contiguous(), idx2.contiguous(), g2[:, lo2:hi2], g1)
+    else:
+        own1 = torch.zeros(xyz1.size(0), hi1 - lo1, 3, dtype=xyz1.dtype, device=xyz1.device)
+        own2 = torch.zeros(xyz2.size(0), hi2 - lo2, 3, dtype=xyz2.dtype, device=xyz2.device)
+        compute.backward_term(xyz1[:, lo1:hi1].contiguous(), xyz2, graddist1.contiguous(), idx1.contiguous(), own1, g2)
+        compute.backward_term(xyz2[:, lo2:hi2].contiguous(), xyz1, graddist2.contiguous(), idx2.contiguous(), own2, g1)
+        g1[:, lo1:hi1] += own1
+        g2[:, lo2:hi2] += own2
+    _mark("backward: zero-fill + both gradient terms", xyz1)
     if info.world > 1:
         dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        _mark("all_reduce(SUM) gradients", xyz1)
     return g1, g2
 
 

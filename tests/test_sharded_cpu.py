@@ -41,7 +41,7 @@ class OracleCompute:
     def rows(xyz1, xyz2, lo, hi):
         import oracle
 
-        assert lo % GROUP == 0 and (hi % GROUP == 0 or hi == xyz1.size(1))
+        assert (lo % GROUP == 0 or lo == xyz1.size(1)) and (hi % GROUP == 0 or hi == xyz1.size(1))
         b, m = xyz1.size(0), xyz2.size(1)
         per = (m + TT - 1) // TT * TT
         keys = np.full((b, per), KEY_INIT, np.int64)
@@ -168,6 +168,21 @@ def test_shard_ranges_cover_and_balance():
                 assert all(lo % align == 0 for lo, _ in r)
                 sizes = [hi - lo for lo, hi in r]
                 assert min(sizes) >= 0 and max(sizes) - min(sizes) <= (1 if align == 1 else 2 * align)
+
+
+def test_uniform_shard_ranges_have_one_stride():
+    """Cloud-1 row shards: a common stride, so the all_gather of the shards is the full array cut at n."""
+    from pointcloudregistration_b200.sharded import shard_stride, uniform_shard_range
+
+    for n in (0, 1, 7, 8, 10, 1_000_000, 1_000_003):
+        for w in (1, 2, 3, 4, 8):
+            for align in (1, 8):
+                stride = shard_stride(n, w, align)
+                r = [uniform_shard_range(n, w, k, align) for k in range(w)]
+                assert stride % align == 0 and stride * w >= n
+                assert r[0][0] == 0 and r[-1][1] == n and all(r[k][1] == r[k + 1][0] for k in range(w - 1))
+                assert all(lo == min(n, k * stride) and hi - lo <= stride for k, (lo, hi) in enumerate(r))
+    assert uniform_shard_range(1_000_000, 8, 3, 8) == (375_000, 500_000)
 
 
 def test_single_process_without_process_group():
