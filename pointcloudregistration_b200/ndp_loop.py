@@ -112,3 +112,166 @@ class ChamferLoopFunction(Function):
     def backward(ctx, g):
         (grad_x,) = ctx.saved_tensors
         return (grad_x * g).reshape(ctx.shape), None
+
+
+class _StaticChamfer(Function):
+    """loss = truncated chamfer(x_warped, target) over STATIC buffers through the C ABI -- the piece of
+    GraphedIteration that sits between the warp network's forward and its backward.  Everything it launches is
+    capturable (no allocation, no host read): nnd forward, the fused mean/mean epilogue (which also leaves
+    d loss / d dist), and in backward the nnd backward (deterministic variant when enabled)."""
+
+    @staticmethod
+    def forward(ctx, x, st):
+        lib, dev = st.lib, st.device
+        b, n, m = st.b, st.n, st.m
+        st.x.copy_(x.reshape(b, n, 3))
+        sp = _stream_ptr(dev)
+        rc = lib.nnd_forward_cuda_f32(st.x.data_ptr(), st.y.data_ptr(), b, n, m, st.dist1.data_ptr(), st.dist2.data_ptr(),
+                                      st.idx1.data_ptr(), st.idx2.data_ptr(), st._ws.data_ptr(), st._ws.numel(), sp)
+        _cabi.check(rc, "nnd_forward_cuda_f32")
+        s1, s2 = 1.0 / (max(n, 1) * max(b, 1)), 1.0 / (max(m, 1) * max(b, 1))
+        rc = lib.nnd_chamfer_reduce_cuda_f32(st.dist1.data_ptr(), st.dist2.data_ptr(), b, n, m, st.trunc, s1, s2,
+                                             st.loss.data_ptr(), st._gd1.data_ptr(), st._gd2.data_ptr(),
+                                             st._rws.data_ptr(), st._rws.numel(), sp)
+        _cabi.check(rc, "nnd_chamfer_reduce_cuda_f32")
+        ctx.st, ctx.shape = st, x.shape
+        return st.loss.clone()
+
+    @staticmethod
+    def backward(ctx, g):
+        st = ctx.st
+        lib, dev = st.lib, st.device
+        b, n, m = st.b, st.n, st.m
+        sp = _stream_ptr(dev)
+        if st.exact:
+            rc = lib.nnd_backward_exact_cuda_f32(st.x.data_ptr(), st.y.data_ptr(), st._gd1.data_ptr(), st._gd2.data_ptr(),
+                                                 st.idx1.data_ptr(), st.idx2.data_ptr(), b, n, m, st.grad_x.data_ptr(),
+                                                 st.grad_y.data_ptr(), st._ews.data_ptr(), st._ews.numel(), sp)
+            _cabi.check(rc, "nnd_backward_exact_cuda_f32")
+        else:
+            rc = lib.nnd_backward_cuda_f32(st.x.data_ptr(), st.y.data_ptr(), st._gd1.data_ptr(), st._gd2.data_ptr(),
+                                           st.idx1.data_ptr(), st.idx2.data_ptr(), b, n, m, st.grad_x.data_ptr(),
+                                           st.grad_y.data_ptr(), sp)
+            _cabi.check(rc, "nnd_backward_cuda_f32")
+        return (st.grad_x * g).reshape(ctx.shape), None
+
+
+class GraphedIteration:
+    """The WHOLE iteration of the reference's non-rigid stage (registration.py:231-261) as one CUDA graph:
+
+        s_warped = warp(source)                                           registration.py:232  (any nn.Module / callable)
+        loss     = compute_truncated_chamfer_distance(s_warped, target)   registration.py:236  (+ extra_loss(), e.g. the
+                                                                          w_reg BCE term of :241-245)
+        optimizer.zero_grad(); loss.backward(); optimizer.step()          registration.py:258-260
+
+    The reference reads loss.item() twice per iteration for its early-stop test (registration.py:250-256): a host
+    synchronisation per iteration, which at the real ~3 k-point size dominates the iteration.  Here the loss stays on the
+    device; run() applies the SAME stop rules (loss < 1e-4; break_counter of relative changes below the threshold) but
+    reads the loss every `read_every`-th iteration only.
+
+    warp's parameters are optimised in place by `optimizer` (built by the caller, e.g. torch.optim.Adam(params,
+    lr=..., capturable=True) as torch requires for graph capture).  `use_graph=False` runs the identical sequence
+    eagerly (the comparison path of the tests).  exact=True takes the deterministic backward (bit-reproducible runs)."""
+
+    def __init__(self, warp, optimizer, source: torch.Tensor, target: torch.Tensor, trunc: float = 1e9,
+                 extra_loss=None, use_graph: bool = True, exact: bool = False):
+        dev = source.device
+        if dev.type != "cuda":
+            raise RuntimeError("GraphedIteration needs CUDA tensors: pointcloudregistration_b200 has no CPU path")
+        n, m = source.shape[-2], target.shape[-2]
+        self.st = st = ChamferLoop(1, n, m, dev, trunc=trunc, use_graph=False)
+        st.exact = bool(exact)
+        if st.exact:
+            nbytes = st.lib.nnd_backward_exact_workspace_bytes(1, n, m)
+            st._ews = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=dev)
+        st.set_target(target)
+        self.warp, self.optimizer, self.extra_loss = warp, optimizer, extra_loss
+        self.source = source.detach().reshape(n, 3).clone()
+        self.warped = torch.zeros_like(self.source)
+        self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self.use_graph, self.graph = use_graph, None
+        self.iterations = 0
+
+    def _body(self):
+        self.optimizer.zero_grad(set_to_none=False)
+        y = self.warp(self.source)
+        loss = _StaticChamfer.apply(y, self.st)
+        if self.extra_loss is not None:
+            loss = loss + self.extra_loss()
+        loss.backward()
+        self.optimizer.step()
+        self.warped.copy_(y.detach())
+        self.loss.copy_(loss.detach())
+
+    def _capture(self):
+        dev = self.source.device
+        # torch's recipe for whole-step capture: a few eager iterations on a side stream first (lazy initialisation of
+        # cuBLAS handles, optimizer state, our func attributes), with parameters and optimizer state restored afterwards
+        # so that the captured run starts from the caller's state
+        params = [p for g in self.optimizer.param_groups for p in g["params"]]
+        saved = [p.detach().clone() for p in params]
+        saved_opt = self.optimizer.state_dict()
+        import copy
+
+        saved_opt = copy.deepcopy(saved_opt)
+        s = torch.cuda.Stream(dev)
+        s.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(s):
+            for g in self.optimizer.param_groups:
+                for p in g["params"]:
+                    if p.grad is None:
+                        p.grad = torch.zeros_like(p)
+            for _ in range(3):
+                self._body()
+        torch.cuda.current_stream(dev).wait_stream(s)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._body()
+        with torch.no_grad():  # the warm-up and the capture pass moved the parameters: put the caller's state back
+            for p, v in zip(params, saved):
+                p.copy_(v)
+            live = self.optimizer.state_dict()["state"]
+            for k, stt in saved_opt["state"].items():
+                for name, v in stt.items():
+                    if torch.is_tensor(v):
+                        live[k][name].copy_(v)
+            if not saved_opt["state"]:  # fresh optimizer: zero the moments and the step counters the warm-up created
+                for stt in live.values():
+                    for v in stt.values():
+                        if torch.is_tensor(v):
+                            v.zero_()
+
+    def step(self):
+        """One iteration; no host synchronisation.  self.loss / self.warped hold its loss and warped source."""
+        with torch.cuda.device(self.source.device):
+            if not self.use_graph:
+                for g in self.optimizer.param_groups:
+                    for p in g["params"]:
+                        if p.grad is None:
+                            p.grad = torch.zeros_like(p)
+                self._body()
+            else:
+                if self.graph is None:
+                    self._capture()
+                self.graph.replay()
+        self.iterations += 1
+
+    def run(self, iters: int, read_every: int = 10, loss_tol: float = 1e-4, break_threshold_ratio: float = 1e-4,
+            max_break_count: int = 15):
+        """The loop of registration.py:210-260 with its early-stop rules evaluated on every read_every-th loss.
+        Returns the list of (iteration, loss) pairs that were read."""
+        hist, loss_prev, break_counter = [], 1e6, 0
+        for it in range(iters):
+            self.step()
+            if it % read_every == 0 or it == iters - 1:
+                val = float(self.loss.item())
+                hist.append((it, val))
+                if val < loss_tol:
+                    break
+                if abs(loss_prev - val) < loss_prev * break_threshold_ratio:
+                    break_counter += 1
+                if break_counter >= max_break_count:
+                    break
+                loss_prev = val
+        return hist

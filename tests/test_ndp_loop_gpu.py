@@ -90,3 +90,56 @@ def test_fused_reduce_matches_float64_numpy(cuda_lib, device, b, n, m):
         d1 = d1.nan_to_num(0.1)  # second and third rounds: finite
     ws.fill_(0xff)
     F.chamfer_reduce_raw(d1.to(device), d2.to(device), trunc, s1, s2, loss, None, None, ws)  # no gradient wanted
+
+
+class _Warp(torch.nn.Module):
+    """A small stand-in for one NDP pyramid level (nets.py:66-143 is out of scope): x + MLP(x)."""
+
+    def __init__(self, width=64):
+        super().__init__()
+        self.net = torch.nn.Sequential(torch.nn.Linear(3, width), torch.nn.ReLU(), torch.nn.Linear(width, width),
+                                       torch.nn.ReLU(), torch.nn.Linear(width, 3))
+        with torch.no_grad():
+            self.net[-1].weight.mul_(0.01)
+
+    def forward(self, x):
+        return x + self.net(x)
+
+
+def _iteration(n, m, seed, device, use_graph, exact=True):
+    torch.manual_seed(seed)
+    warp = _Warp().to(device)
+    opt = torch.optim.Adam(warp.parameters(), lr=1e-3, capturable=True)
+    x0, y = synthetic.make_pair("clustered", 1, n, m, seed)
+    return ndp_loop.GraphedIteration(warp, opt, x0[0].to(device) + 0.05, y[0].to(device), trunc=1e9,
+                                     use_graph=use_graph, exact=exact), warp
+
+
+@pytest.mark.parametrize("n,m", [(3000, 2900), (100_000, 100_000)])
+def test_whole_iteration_graph_matches_the_eager_loop_for_500_iterations(cuda_lib, device, n, m):
+    """warp MLP forward -> chamfer -> backward -> Adam step captured as ONE CUDA graph (registration.py:231-261) against
+    the same sequence run eagerly, 500 iterations, deterministic backward on both sides: the loss curve (read every
+    10th iteration, the early-stop protocol) agrees to fp32 rounding and so do the final warped points."""
+    ga, wa = _iteration(n, m, 98, device, use_graph=True)
+    gb, wb = _iteration(n, m, 98, device, use_graph=False)
+    for pa, pb in zip(wa.parameters(), wb.parameters()):
+        assert torch.equal(pa, pb)
+    ha = ga.run(500, read_every=10, loss_tol=0.0, break_threshold_ratio=0.0)
+    hb = gb.run(500, read_every=10, loss_tol=0.0, break_threshold_ratio=0.0)
+    assert len(ha) == len(hb) == 51 and ga.iterations == 500
+    for (ia, la), (ib, lb) in zip(ha, hb):
+        assert ia == ib and abs(la - lb) <= 2e-6 * abs(lb), (ia, la, lb)
+    assert ha[-1][1] < 0.9 * ha[0][1]  # it trains
+    assert torch.allclose(ga.warped, gb.warped, rtol=0, atol=2e-6)
+    for pa, pb in zip(wa.parameters(), wb.parameters()):
+        assert torch.allclose(pa, pb, rtol=1e-4, atol=1e-6)
+
+
+def test_whole_iteration_early_stop_protocol(cuda_lib, device):
+    """run() applies registration.py:250-256's rules on the losses it reads: stops once the loss is below the
+    tolerance, and the atomic backward (default) trains too."""
+    g, _ = _iteration(2000, 2000, 99, device, use_graph=True, exact=False)
+    hist = g.run(300, read_every=10, loss_tol=1e9)  # any loss is below 1e9: stops at the first read
+    assert len(hist) == 1 and g.iterations == 1
+    hist = g.run(200, read_every=20, loss_tol=0.0, break_threshold_ratio=0.0)
+    assert [it for it, _ in hist] == list(range(0, 200, 20)) + [199] and hist[-1][1] < hist[0][1]
