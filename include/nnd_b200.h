@@ -193,7 +193,8 @@ long long nnd_set_panel_min_rows(long long rows);
  * whose stream is being captured into a CUDA graph always takes the persistent kernel (results are bit-identical). */
 int nnd_rows_scan_kind(int b, int n, int m, int row_lo, int row_hi);
 /* Tuning knob: sample tiles (512 rows each) of the column-filter seed pass run in front of the PERSISTENT symmetric kernel
- * (0 = off, the default; the panel scan always seeds).  Returns the previous value; negative only queries. */
+ * (default 1; 0 = off; the panel scan always seeds).  Results do not depend on it.  Returns the previous value; negative
+ * only queries. */
 int nnd_set_sym_seed_tiles(int tiles);
 /* Column tiles (512 points) per panel launch: 0 = chosen from the row count (default), 1, 2 or 4 = forced.  Returns the
  * previous setting; other values only query.  Environment: NND_B200_PANEL_TILES. */

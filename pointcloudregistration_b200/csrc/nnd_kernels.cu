@@ -734,7 +734,11 @@ void launch_scan(const ScanParams& sp, int grid, cudaStream_t st) {
 }
 
 inline bool use_symmetric(int n, int m);
-std::atomic<int> g_sym_seed{0};  // sample tiles of the filter seed in front of the persistent symmetric kernel (0 = off)
+// Sample tiles (512 rows each) of the column-filter seed run in front of the persistent symmetric kernel.  One tile
+// costs 512 / rows of the scan and removes the cold-filter start (every first-wave warp step taking the column slow
+// path): measured forward, profiles/r02_sym_seed_ab.txt / r02_panel_threshold_ab.txt: N=M=150 000 8.78 -> 6.51 ms,
+// 32 768 0.482 -> 0.429 ms, 65 536 1.404 -> 1.285 ms, C2 2.75 -> 2.69 ms, C3 2.91 -> 2.88 ms; more tiles lose again.
+std::atomic<int> g_sym_seed{1};
 // Shape of the symmetric kernel: the large one whenever the single-GPU entry point would pick the symmetric path
 // (more rows per warp step = fewer column slow paths); small clouds only get here through the row-range entry point.
 inline ScanShape sym_shape(int b, int n, int m, int sms) {
@@ -924,8 +928,7 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   const int grid = yp.total_units < grid_full ? (int)yp.total_units : grid_full;
   const size_t smem = sizeof(SymStage<kTT>) * kStages + (size_t)si.threads * si.qpt * 8;  // ring + row bookkeeping
   const bool panels = path == kRowsPanel;
-  // Tuning knob (nnd_set_sym_seed_tiles): run the panel path's filter seed in front of the
-  // persistent kernel as well (fewer column slow-path entries on mid-sized clouds for ~ TT / rows extra work).
+  // The panel path's filter seed in front of the persistent kernel as well (nnd_set_sym_seed_tiles; default 1 tile).
   const int sym_seed = g_sym_seed.load(std::memory_order_relaxed);
   if (!panels && sym_seed > 0 && shape == kShapeLarge) {
     const int t_first = (row_lo + kTT - 1) / kTT;

@@ -36,4 +36,4 @@ for name, b, n, cfg in (("C2", 32, 16384, 2), ("C3", 1, 100_000, 3), ("B=1 N=M=3
         best, mean = min(ts), sum(ts) / len(ts)
         print(f"{name:16s} seed tiles {tiles}: forward best {best:8.4f} ms  mean {mean:8.4f} ms  "
               f"{b * n * n * 8 / (best * 1e-3) / PEAK * 100:5.1f}% of the FP32 issue peak (evaluations executed)", flush=True)
-    lib.nnd_set_sym_seed_tiles(0)
+    lib.nnd_set_sym_seed_tiles(1)
