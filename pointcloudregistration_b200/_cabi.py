@@ -12,8 +12,11 @@ from pathlib import Path
 
 import os
 
-# NND_B200_LIB: developer override to time an experimental build of the same ABI (tools/variants.sh)
-LIB_PATH = Path(os.environ.get("NND_B200_LIB") or Path(__file__).resolve().parent / "libnnd_b200.so")
+# The product always loads the library that sits next to this file.  NND_B200_LIB (an experimental build of the same
+# ABI, tools/variants.sh) is honoured ONLY together with NND_B200_DEBUG=1, and load() says so on stderr: a stray
+# environment variable must not silently redirect the product to another library.
+_override = os.environ.get("NND_B200_LIB") if os.environ.get("NND_B200_DEBUG") == "1" else None
+LIB_PATH = Path(_override or Path(__file__).resolve().parent / "libnnd_b200.so")
 
 #: every symbol include/nnd_b200.h declares -> (restype, argtypes)
 SIGNATURES = {
@@ -81,6 +84,10 @@ def load():
         raise NNDLibraryError(
             f"{LIB_PATH} is missing. Build it with `python -c 'import __graft_entry__ as g; g.build()'` "
             "(nvcc, sm_100a). There is no CPU fallback for nnd.")
+    if _override:
+        import sys
+
+        print(f"[nnd_b200] NND_B200_DEBUG=1: loading {LIB_PATH} instead of the packaged library", file=sys.stderr)
     lib = ctypes.CDLL(str(LIB_PATH))
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the header and the library disagree

@@ -1,6 +1,10 @@
 """CPU tests of the host-side mirror of the reference interface (names, validation, error behaviour)."""
+from pathlib import Path
+
 import pytest
 import torch
+
+ROOT = Path(__file__).resolve().parent.parent
 
 
 def test_drop_in_names_exist():
@@ -84,3 +88,28 @@ def test_exact_backward_switch_follows_torch_deterministic_mode():
     finally:
         F.set_exact_backward(None)
         torch.use_deterministic_algorithms(before)
+
+
+def test_library_override_needs_the_debug_flag(tmp_path):
+    """NND_B200_LIB alone must not redirect the product to another library; with
+    NND_B200_DEBUG=1 it does, for timing experimental builds of the same ABI."""
+    import os
+    import subprocess
+    import sys
+
+    code = "from pointcloudregistration_b200 import _cabi; print(_cabi.LIB_PATH)"
+    env = dict(os.environ, NND_B200_LIB=str(tmp_path / "other.so"), PYTHONPATH=str(ROOT))
+    env.pop("NND_B200_DEBUG", None)
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, check=True).stdout
+    assert out.strip().endswith("pointcloudregistration_b200/libnnd_b200.so")
+    env["NND_B200_DEBUG"] = "1"
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, check=True).stdout
+    assert out.strip() == str(tmp_path / "other.so")
+
+
+def test_packaging_metadata_names_the_drop_in_modules():
+    """pyproject.toml installs the three import names the reference's `python build.py install` provided."""
+    text = (ROOT / "pyproject.toml").read_text()
+    for name in ("pointcloudregistration_b200", "torch_nndistance", "torch_nndistance_aten", "libnnd_b200.so"):
+        assert name in text
+    assert "build_library" in (ROOT / "setup.py").read_text()

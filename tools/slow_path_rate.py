@@ -1,5 +1,5 @@
 """Dev tool (GPU box): fraction of 4-target warp steps of nnd_scan_sym_kernel that enter the column slow path.
-Needs a -DNND_SYM_COUNT build:  tools/variants.sh "count:-DNND_SYM_COUNT" ; NND_B200_LIB=tools/variants/libnnd_count.so"""
+Needs a -DNND_SYM_COUNT build:  tools/variants.sh "count:-DNND_SYM_COUNT" ; NND_B200_DEBUG=1 NND_B200_LIB=tools/variants/libnnd_count.so"""
 import ctypes
 import math
 import sys

@@ -6,6 +6,6 @@ mkdir -p "$out"
 for v in "$@"; do
   lib=$PWD/tools/variants/libnnd_$v.so
   echo "=== variant $v" | tee -a "$out/summary.txt"
-  NND_B200_LIB=$lib timeout 600 python -m pytest tests/test_nnd_gpu.py -x -q -m gpu 2>&1 | tail -2 | tee -a "$out/summary.txt"
-  NND_B200_LIB=$lib timeout 600 python tools/quick_time.py $args 2>&1 | grep -v clustered | tee -a "$out/summary.txt"
+  NND_B200_DEBUG=1 NND_B200_LIB=$lib timeout 600 python -m pytest tests/test_nnd_gpu.py -x -q -m gpu 2>&1 | tail -2 | tee -a "$out/summary.txt"
+  NND_B200_DEBUG=1 NND_B200_LIB=$lib timeout 600 python tools/quick_time.py $args 2>&1 | grep -v clustered | tee -a "$out/summary.txt"
 done
