@@ -567,6 +567,42 @@ def e2e_region(r, steps, warmup, barrier):
     return float(ms.item()) / steps, last, h2d, d2h
 
 
+def e2e_graph_region(r, steps, warmup):
+    """End to end through the repo's OTHER public entry point for repeated chamfer on fixed-size clouds,
+    ndp_loop.ChamferLoop (forward + mean/mean chamfer epilogue + backward replayed as one CUDA graph): every step
+    copies both clouds from PINNED HOST buffers into the loop's static inputs, replays, and copies both gradients and
+    the loss back to the host.  Same work and same bytes as e2e_region, without autograd's per-step host cost."""
+    from pointcloudregistration_b200 import ndp_loop
+
+    torch, dev = r.torch, r.dev
+    b, n, m = r.b, r.n, r.m
+    loop = ndp_loop.ChamferLoop(b, n, m, dev, trunc=float("inf"))
+    g1h = torch.empty(b, n, 3, dtype=torch.float32).pin_memory()
+    g2h = torch.empty(b, m, 3, dtype=torch.float32).pin_memory()
+    lossh = torch.empty((), dtype=torch.float32).pin_memory()
+
+    def step():
+        loop.y.copy_(r.x2h, non_blocking=True)
+        loop.step(r.x1h)  # copies x (pinned host -> static device buffer) and replays the graph
+        g1h.copy_(loop.grad_x, non_blocking=True)
+        g2h.copy_(loop.grad_y, non_blocking=True)
+        lossh.copy_(loop.loss, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(lossh)
+
+    last = None
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        last = step()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps, last
+
+
 def other_config(key, kind, world, rank, dev, lib, fp32_peak, digests, flush, barrier, want_e2e, want_graph):
     """One of the non-headline configs: a few timed steps with the headline's protocol, its roofline fraction and its
     own parity record."""
@@ -598,7 +634,12 @@ def other_config(key, kind, world, rank, dev, lib, fp32_peak, digests, flush, ba
     if want_e2e:
         ems, loss, h2d, d2h = e2e_region(r, 40 if tiny else 3, 5 if tiny else 2, barrier)
         rec["e2e"] = {"value": r.pairs / (ems * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": ems, "loss": loss,
-                      "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h}
+                      "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "api": "torch_nndistance.nnd + autograd"}
+        if world == 1:
+            gms, gloss = e2e_graph_region(r, 40 if tiny else 3, 5 if tiny else 2)
+            rec["e2e_graph"] = {"value": r.pairs / (gms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": gms, "loss": gloss,
+                                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                                "api": "ndp_loop.ChamferLoop (one CUDA-graph replay per step; host buffers in and out)"}
     return rec, r
 
 
@@ -748,8 +789,9 @@ def run_b200_arm(args, w):
             if ref and "ms_per_step" in ref:
                 rec["reference_cuda_ms_per_step"] = ref["ms_per_step"]
                 rec["speedup_vs_reference_cuda"] = ref["ms_per_step"] / rec["ms_per_step"]
-                if "e2e" in rec:
-                    rec["e2e_speedup_vs_reference_cuda_device_time"] = ref["ms_per_step"] / rec["e2e"]["ms_per_step"]
+                for kk in ("e2e", "e2e_graph"):  # the reference's step has no host copies in it: a conservative ratio
+                    if kk in rec:
+                        rec[kk]["speedup_vs_reference_cuda_resident_step"] = ref["ms_per_step"] / rec[kk]["ms_per_step"]
 
     if rank == 0:
         # One launch of the symmetric scan kernel evaluates every (xyz1[j], xyz2[k]) distance of its row range

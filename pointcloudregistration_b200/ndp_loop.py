@@ -78,11 +78,11 @@ class ChamferLoop:
             self._body()
 
     def set_target(self, y: torch.Tensor) -> None:
-        self.y.copy_(y.detach().reshape(self.b, self.m, 3))
+        self.y.copy_(y.detach().reshape(self.b, self.m, 3), non_blocking=True)
 
     def step(self, x: torch.Tensor):
         """loss (0-dim device tensor, valid until the next step) and d loss / d x [b,n,3]; no host sync."""
-        self.x.copy_(x.detach().reshape(self.b, self.n, 3))
+        self.x.copy_(x.detach().reshape(self.b, self.n, 3), non_blocking=True)  # stream-ordered, also from pinned host memory
         with torch.cuda.device(self.device):
             if not self.use_graph:
                 self._body()
