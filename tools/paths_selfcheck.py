@@ -29,16 +29,38 @@ def say(msg):
     print("[selfcheck]", msg, flush=True)
 
 
-# two-pass kernel (small clouds), all three work shapes + the one-direction entry point
-for b, n, m in ((2, 300, 700), (1, 2048, 1024), (40, 64, 70)):
-    x1, x2 = (t.to(dev) for t in synthetic.make_pair("crosscopy", b, n, m, 7))
-    d1, d2, i1, i2 = F.nnd_forward_raw(x1, x2)
-    dq, iq = F.nnd_query_raw(x1, x2)
-    same((d1, i1), (dq, iq), "query != forward")
-    gd1, gd2 = (t.to(dev) for t in synthetic.grad_pair(b, n, m, 7))
-    F.nnd_backward_raw(x1, x2, gd1, gd2, i1, i2)
-    torch.cuda.synchronize()
-    say(f"two-pass b={b} n={n} m={m} ok")
+# small clouds: the single-launch kernels (default) and, with that path switched off, the two-pass kernel in all three
+# work shapes + the one-direction entry point + both backward paths
+for small_max in (-1, 0):
+    keep = lib.nnd_set_small_max_points(small_max)
+    for b, n, m in ((2, 300, 700), (1, 2048, 1024), (40, 64, 70), (1, 5000, 4100)):
+        x1, x2 = (t.to(dev) for t in synthetic.make_pair("crosscopy", b, n, m, 7))
+        d1, d2, i1, i2 = F.nnd_forward_raw(x1, x2)
+        dq, iq = F.nnd_query_raw(x1, x2)
+        same((d1, i1), (dq, iq), "query != forward")
+        gd1, gd2 = (t.to(dev) for t in synthetic.grad_pair(b, n, m, 7))
+        F.nnd_backward_raw(x1, x2, gd1, gd2, i1, i2)
+        torch.cuda.synchronize()
+        say(f"{'single-launch' if lib.nnd_forward_kind(b, n, m) == 0 else 'two-pass'} b={b} n={n} m={m} ok")
+    lib.nnd_set_small_max_points(keep)
+# every configuration of the single-launch forward, and a ragged batch (lengths read by the kernels)
+x1, x2 = (t.to(dev) for t in synthetic.make_pair("lattice", 3, 700, 900, 9))
+ref_small = F.nnd_forward_raw(x1, x2)
+for w in (4, 8, 16):
+    for q in (1, 2):
+        for t in (1, 2, 4, 8, 16):
+            if w % t == 0:
+                lib.nnd_set_small_config(w, q, t)
+                same(F.nnd_forward_raw(x1, x2), ref_small, f"small config {w},{q},{t}")
+lib.nnd_set_small_config(0, 0, 0)
+l1, l2 = torch.tensor([700, 13, 0], device=dev), torch.tensor([900, 1, 5], device=dev)
+rd = F.nnd_forward_ragged_raw(x1, x2, l1, l2)
+gd1, gd2 = (t.to(dev) for t in synthetic.grad_pair(3, 700, 900, 9))
+F.nnd_backward_ragged_raw(x1, x2, gd1, gd2, rd[2], rd[3], l1, l2)
+F.nnd_knn_backward_ragged_raw(x1, x2, gd1, rd[2], l1, l2)
+torch.cuda.synchronize()
+say("single-launch configurations + ragged batch ok")
+keep_small = lib.nnd_set_small_max_points(0)  # the sections below are about the general paths
 
 # persistent symmetric kernel, then the same problem through the panel kernel (1, 2, 4 tiles per panel) and through
 # row ranges (normal and role-swapped): all bit-identical
@@ -87,3 +109,4 @@ loss.backward()
 torch.cuda.synchronize()
 say(f"fused chamfer epilogue ok, loss {loss.item():.6e}")
 say("ALL OK")
+lib.nnd_set_small_max_points(keep_small)
