@@ -456,6 +456,14 @@ constexpr int kTT = NND_TT;
 #define NND_CHUNK 32
 #endif
 constexpr int kChunk = NND_CHUNK;
+#ifndef NND_SYMC_CHUNK
+#define NND_SYMC_CHUNK NND_CHUNK
+#endif
+constexpr int kSymcChunk = NND_SYMC_CHUNK;  // lazy-index chunk of the panel scan
+#ifndef NND_SYMC_SKIP
+#define NND_SYMC_SKIP 4
+#endif
+constexpr int kSymcFinChunk = NND_SYMC_SKIP * NND_SYMC_CHUNK;  // ... and of the finalize that follows it
 constexpr int kStages = NND_STAGES;
 constexpr int kMinBlocks = NND_MINB;
 constexpr int kQB = kThreads * kQPT;
@@ -676,9 +684,9 @@ int scan_panels_pt(SymCParams yp, const float* soa2, int b, int qblocks, PanelCt
       if (e != cudaSuccess) return (int)e;
       const bool full = yp.ntiles == PT && (tile_lo + PT) * kTT <= yp.m;
       if (full)
-        nnd_scan_symc_kernel<THREADS, QPT, kTT, kChunk, kMinBlocks, PT, true><<<qblocks, THREADS, smem, c->s[which]>>>(yp);
+        nnd_scan_symc_kernel<THREADS, QPT, kTT, kSymcChunk, kMinBlocks, PT, true><<<qblocks, THREADS, smem, c->s[which]>>>(yp);
       else
-        nnd_scan_symc_kernel<THREADS, QPT, kTT, kChunk, kMinBlocks, PT, false><<<qblocks, THREADS, smem, c->s[which]>>>(yp);
+        nnd_scan_symc_kernel<THREADS, QPT, kTT, kSymcChunk, kMinBlocks, PT, false><<<qblocks, THREADS, smem, c->s[which]>>>(yp);
       ++g_launches;
     }
   }
@@ -839,7 +847,7 @@ int forward_rows_swapped_impl(const float* c1, int n1, const float* c2, int n2, 
   fp.d[0] = FinDir{keysR, c2, soaS, nullptr, nullptr, n2, tiles_of(nrows), 0, n2, (long long)b * n2,
                    colkeys, (long long)tiles_of(n2) * kTT, row_lo,
                    kShapes[sym_shape(b, n1, n2, di.sms)].qpt};  // the row-group size finalize_cols_impl will assume
-  nnd_finalize_kernel<kTT, kChunk><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
+  nnd_finalize_kernel<kTT, kSymcFinChunk><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
   ++g_launches;
   // range rows -> nearest xyz2 point (complete): dist1 / idx1 of rows [row_lo, row_hi)
   FinColParams fc{ckeysS, c2, c1, dist1, idx1, n2, nrows, tiles_of(nrows), (long long)b * nrows, 1.0f, n1, row_lo};
@@ -980,7 +988,10 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   fp.ndir = 1;
   fp.one = 1.0f;
   fp.d[0] = FinDir{rkeys, c1, soa2, dist1, idx1, n1, tiles_of(n2), row_lo, nrows, (long long)b * nrows};
-  nnd_finalize_kernel<kTT, kChunk><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
+  if (panels)
+    nnd_finalize_kernel<kTT, kSymcFinChunk><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
+  else
+    nnd_finalize_kernel<kTT, kChunk><<<grid_for(fp.d[0].count, di.sms), 256, 0, st>>>(fp);
   ++g_launches;
   if (ev) cudaEventRecord(ev[3], st);
   debug_sync("finalize_rows", st);

@@ -21,6 +21,15 @@
 #ifndef NND_TT
 #define NND_TT 512
 #endif
+// Row bookkeeping (did this chunk improve a row? then remember where) runs after every NND_SYMC_SKIP-th 32-target chunk
+// only; nnd_finalize_kernel then re-scans SKIP * 32 targets per row, which is nothing at the sizes this kernel serves.
+// Measured at C4 (profiles/r02_ab_symc_skip.txt): 254.22 ms with 1, 253.53 with 2, 253.17 with 4, 253.2-253.8 with 8.
+// Also measured, all worse (r02_ab_symc_chunk.txt, r02_ab_symc_chunk2.txt): a 64-target chunk (+16 %: the unrolled body
+// no longer fits the instruction cache), a 16-target chunk (+2 %), the chunk loop unrolled 4 or 2 steps instead of 8
+// (+0.7 / +1 %), the previous minima in registers instead of shared memory (+0.6 %).
+#ifndef NND_SYMC_SKIP
+#define NND_SYMC_SKIP 4
+#endif
 // The 48 KB constant window is cut into 2 buffers of 4 tiles, 4 of 2 or 8 of 1: fewer rows per launch (one CTA per
 // row block) want more launches in flight to keep 2 CTAs on every SM.
 constexpr int kPanelFloats = 8 * 3 * NND_TT;  // 8 tiles x 6 KB = 48 KB of the 64 KB constant bank
@@ -53,8 +62,13 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_symc_kernel(const __gr
   constexpr unsigned FULLMASK = 0xffffffffu;
   extern __shared__ __align__(128) unsigned char symc_smem[];
   unsigned* filt = reinterpret_cast<unsigned*>(symc_smem);  // [PT * TT]
+#ifdef NND_SYMC_PREV_REG  // experiment: previous row minima in registers, only the chunk base in shared memory
+  int* sbase = reinterpret_cast<int*>(filt + PT * TT) + threadIdx.x;
+  float prevr[QPT];
+#else
   float* sprev = reinterpret_cast<float*>(filt + PT * TT) + threadIdx.x;
   int* sbase = reinterpret_cast<int*>(sprev - threadIdx.x + QPT * THREADS) + threadIdx.x;
+#endif
 
   const int tid = threadIdx.x;
   const unsigned lane = tid & 31u;
@@ -84,7 +98,11 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_symc_kernel(const __gr
     nqy[q] = pk2(y, y);
     nqz[q] = pk2(z, z);
     cm[q] = INF;
+#ifdef NND_SYMC_PREV_REG
+    prevr[q] = INF;
+#else
     sprev[q * THREADS] = INF;
+#endif
     sbase[q * THREADS] = 0;
   }
   __syncthreads();
@@ -101,7 +119,12 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_symc_kernel(const __gr
   for (int k0 = 0; k0 < panel_live; k0 += C) {          // one 32-target chunk per iteration
     const int tl = k0 / TT, ko = k0 - tl * TT;          // local tile, offset inside the tile
     const float* cx = cpanel + tl * (3 * TT) + ko;
-#pragma unroll
+#ifdef NND_SYMC_UNROLL  // experiment: partially unrolled chunk (smaller loop body)
+    constexpr int kSteps = NND_SYMC_UNROLL;
+#else
+    constexpr int kSteps = C / 4;
+#endif
+#pragma unroll kSteps
     for (int s4 = 0; s4 < C / 4; ++s4) {
       const ulonglong2 X = *reinterpret_cast<const ulonglong2*>(cx + 4 * s4);
       const ulonglong2 Y = *reinterpret_cast<const ulonglong2*>(cx + TT + 4 * s4);
@@ -132,12 +155,20 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_symc_kernel(const __gr
         sym_column_update(u0, u1, u2, u3, H.x, H.y, H.z, H.w, lane, group, ckeys, cdist, filt, panel_base, kl);
     }
     // end of the chunk: did it improve a row?  (strict <, chunks ascend: the earliest chunk with the minimum stays)
+#if NND_SYMC_SKIP > 1  // row bookkeeping after every NND_SYMC_SKIP-th chunk (the finalize re-scans SKIP * C targets)
+    if ((kv & ((NND_SYMC_SKIP - 1) * C)) == (NND_SYMC_SKIP - 1) * C || kv + C >= panel_live)  // kv, not k0: a condition
+#endif                                                                            // on the uniform counter costs the LDCUs
 #pragma unroll
     for (int q = 0; q < QPT; ++q) {
+#ifdef NND_SYMC_PREV_REG
+      if (cm[q] < prevr[q]) sbase[q * THREADS] = panel_base + kv;
+      prevr[q] = cm[q];  // cm is the running minimum: it only ever decreases
+#else
       if (cm[q] < sprev[q * THREADS]) {
         sprev[q * THREADS] = cm[q];
-        sbase[q * THREADS] = panel_base + kv;
+        sbase[q * THREADS] = panel_base + (kv & ~((NND_SYMC_SKIP - 1) * C));  // start of the group of chunks
       }
+#endif
     }
     kv += C;
   }
