@@ -201,8 +201,8 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
         const ulonglong2* cx = reinterpret_cast<const ulonglong2*>(sx + ch * C);
         const ulonglong2* cy = reinterpret_cast<const ulonglong2*>(sy + ch * C);
         const ulonglong2* cz = reinterpret_cast<const ulonglong2*>(sz + ch * C);
-#pragma unroll
-        for (int s4 = 0; s4 < C / 4; ++s4) {
+        // one 4-target step: 32 distances, row minima into cm[], column minima of this thread's rows out as bit patterns
+        auto step = [&](int s4, unsigned& u0, unsigned& u1, unsigned& u2, unsigned& u3) {
           const ulonglong2 X = cx[s4], Y = cy[s4], Z = cz[s4];
           float c0 = INF, c1 = INF, c2 = INF, c3 = INF;  // column minima over this thread's rows
 #pragma unroll
@@ -221,12 +221,21 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
             c2 = fmin3(c2, b0, f0);
             c3 = fmin3(c3, b1, f1);
           }
+          u0 = __float_as_uint(c0);
+          u1 = __float_as_uint(c1);
+          u2 = __float_as_uint(c2);
+          u3 = __float_as_uint(c3);
+        };
+        // (One filter test per TWO steps, which gains 0.6 % in the panel kernel, LOSES here: C2 2.68 -> 2.78 ms, C3 2.87 ->
+        // 2.91 ms, profiles/r02_ab_sym_pair.txt -- a quarter of the steps take the slow path at C2, and it is called twice.)
+#pragma unroll
+        for (int s4 = 0; s4 < C / 4; ++s4) {
+          unsigned u0, u1, u2, u3;
+          step(s4, u0, u1, u2, u3);
           // ---- columns: compare with the filter (an upper bound of the column minimum's bit pattern)
           const int koff = ch * C + 4 * s4;
           const uint4 H = *reinterpret_cast<const uint4*>(filt + koff);
           const unsigned h0 = H.x, h1 = H.y, h2 = H.z, h3 = H.w;
-          const unsigned u0 = __float_as_uint(c0), u1 = __float_as_uint(c1);
-          const unsigned u2 = __float_as_uint(c2), u3 = __float_as_uint(c3);
           const bool ev = (u0 <= h0) | (u1 <= h1) | (u2 <= h2) | (u3 <= h3);
           if (__any_sync(FULL, ev)) {
 #ifdef NND_SYM_COUNT

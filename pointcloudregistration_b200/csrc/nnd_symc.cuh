@@ -57,18 +57,13 @@ struct SymCParams {
 // PT: tiles per panel.  FULL: the panel has PT complete tiles (constant trip count).  !FULL: the last, ragged panel of a cloud.
 template <int THREADS, int QPT, int TT, int C, int MINB, int PT, bool FULL>
 __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_symc_kernel(const __grid_constant__ SymCParams p) {
-  static_assert(TT % C == 0 && C % 4 == 0 && QPT % 2 == 0 && TT % QPT == 0, "tile/chunk shape");
+  static_assert(TT % C == 0 && C % 8 == 0 && QPT % 2 == 0 && TT % QPT == 0, "tile/chunk shape");
   constexpr int QB = THREADS * QPT;
   constexpr unsigned FULLMASK = 0xffffffffu;
   extern __shared__ __align__(128) unsigned char symc_smem[];
   unsigned* filt = reinterpret_cast<unsigned*>(symc_smem);  // [PT * TT]
-#ifdef NND_SYMC_PREV_REG  // experiment: previous row minima in registers, only the chunk base in shared memory
-  int* sbase = reinterpret_cast<int*>(filt + PT * TT) + threadIdx.x;
-  float prevr[QPT];
-#else
   float* sprev = reinterpret_cast<float*>(filt + PT * TT) + threadIdx.x;
   int* sbase = reinterpret_cast<int*>(sprev - threadIdx.x + QPT * THREADS) + threadIdx.x;
-#endif
 
   const int tid = threadIdx.x;
   const unsigned lane = tid & 31u;
@@ -98,11 +93,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_symc_kernel(const __gr
     nqy[q] = pk2(y, y);
     nqz[q] = pk2(z, z);
     cm[q] = INF;
-#ifdef NND_SYMC_PREV_REG
-    prevr[q] = INF;
-#else
     sprev[q * THREADS] = INF;
-#endif
     sbase[q * THREADS] = 0;
   }
   __syncthreads();
@@ -119,13 +110,8 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_symc_kernel(const __gr
   for (int k0 = 0; k0 < panel_live; k0 += C) {          // one 32-target chunk per iteration
     const int tl = k0 / TT, ko = k0 - tl * TT;          // local tile, offset inside the tile
     const float* cx = cpanel + tl * (3 * TT) + ko;
-#ifdef NND_SYMC_UNROLL  // experiment: partially unrolled chunk (smaller loop body)
-    constexpr int kSteps = NND_SYMC_UNROLL;
-#else
-    constexpr int kSteps = C / 4;
-#endif
-#pragma unroll kSteps
-    for (int s4 = 0; s4 < C / 4; ++s4) {
+    // one 4-target step: 32 distances, row minima into cm[], column minima of this thread's rows out as bit patterns
+    auto step = [&](int s4, unsigned& u0, unsigned& u1, unsigned& u2, unsigned& u3) {
       const ulonglong2 X = *reinterpret_cast<const ulonglong2*>(cx + 4 * s4);
       const ulonglong2 Y = *reinterpret_cast<const ulonglong2*>(cx + TT + 4 * s4);
       const ulonglong2 Z = *reinterpret_cast<const ulonglong2*>(cx + 2 * TT + 4 * s4);
@@ -146,13 +132,27 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_symc_kernel(const __gr
         c2 = fmin3(c2, b0, f0);
         c3 = fmin3(c3, b1, f1);
       }
-      const int kl = kv + 4 * s4;  // local index of the first of these 4 columns
-      const uint4 H = *reinterpret_cast<const uint4*>(filt + kl);
-      const unsigned u0 = __float_as_uint(c0), u1 = __float_as_uint(c1);
-      const unsigned u2 = __float_as_uint(c2), u3 = __float_as_uint(c3);
-      const bool ev = (u0 <= H.x) | (u1 <= H.y) | (u2 <= H.z) | (u3 <= H.w);
-      if (__any_sync(FULLMASK, ev))
-        sym_column_update(u0, u1, u2, u3, H.x, H.y, H.z, H.w, lane, group, ckeys, cdist, filt, panel_base, kl);
+      u0 = __float_as_uint(c0);
+      u1 = __float_as_uint(c1);
+      u2 = __float_as_uint(c2);
+      u3 = __float_as_uint(c3);
+    };
+    // Two steps share ONE filter test (vote + branch): 251.5 ms against 253.1 at C4 (profiles/r02_ab_symc_pair.txt); the
+    // 8 column minima stay live across the test, which takes the kernel to its 128-register budget, no spills.
+#pragma unroll
+    for (int s4 = 0; s4 < C / 4; s4 += 2) {
+      unsigned a0, a1, a2, a3, b0, b1, b2, b3;
+      step(s4, a0, a1, a2, a3);
+      step(s4 + 1, b0, b1, b2, b3);
+      const int kl = kv + 4 * s4;  // local index of the first of these 8 columns
+      const uint4 HA = *reinterpret_cast<const uint4*>(filt + kl);
+      const uint4 HB = *reinterpret_cast<const uint4*>(filt + kl + 4);
+      const bool ev = (a0 <= HA.x) | (a1 <= HA.y) | (a2 <= HA.z) | (a3 <= HA.w) | (b0 <= HB.x) | (b1 <= HB.y) |
+                      (b2 <= HB.z) | (b3 <= HB.w);
+      if (__any_sync(FULLMASK, ev)) {
+        sym_column_update(a0, a1, a2, a3, HA.x, HA.y, HA.z, HA.w, lane, group, ckeys, cdist, filt, panel_base, kl);
+        sym_column_update(b0, b1, b2, b3, HB.x, HB.y, HB.z, HB.w, lane, group, ckeys, cdist, filt, panel_base, kl + 4);
+      }
     }
     // end of the chunk: did it improve a row?  (strict <, chunks ascend: the earliest chunk with the minimum stays)
 #if NND_SYMC_SKIP > 1  // row bookkeeping after every NND_SYMC_SKIP-th chunk (the finalize re-scans SKIP * C targets)
@@ -160,15 +160,10 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_symc_kernel(const __gr
 #endif                                                                            // on the uniform counter costs the LDCUs
 #pragma unroll
     for (int q = 0; q < QPT; ++q) {
-#ifdef NND_SYMC_PREV_REG
-      if (cm[q] < prevr[q]) sbase[q * THREADS] = panel_base + kv;
-      prevr[q] = cm[q];  // cm is the running minimum: it only ever decreases
-#else
       if (cm[q] < sprev[q * THREADS]) {
         sprev[q * THREADS] = cm[q];
         sbase[q * THREADS] = panel_base + (kv & ~((NND_SYMC_SKIP - 1) * C));  // start of the group of chunks
       }
-#endif
     }
     kv += C;
   }
