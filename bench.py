@@ -530,18 +530,13 @@ def e2e_region(r, steps, warmup, barrier):
     d2h = (g1h.numel() + g2h.numel()) * 4 + 4
 
     def step_e2e():
-        if world == 1 or rank == 0:
-            a = r.x1h.to(dev, non_blocking=True).requires_grad_(True)
-            c = r.x2h.to(dev, non_blocking=True).requires_grad_(True)
-        else:
-            a = torch.empty(b, n, 3, device=dev).requires_grad_(True)
-            c = torch.empty(b, m, 3, device=dev).requires_grad_(True)
+        # every rank holds the step's inputs in its own pinned host memory (one process per GPU, SPMD) and uploads them
+        # itself, in parallel over its own PCIe link: no rank-0 upload followed by an NVLink broadcast
+        a = r.x1h.to(dev, non_blocking=True).requires_grad_(True)
+        c = r.x2h.to(dev, non_blocking=True).requires_grad_(True)
         if world == 1:
             d1, d2 = NND.nnd(a, c)
         else:
-            with torch.no_grad():
-                dist.broadcast(a, src=0)
-                dist.broadcast(c, src=0)
             d1, d2 = sharded.nnd_sharded(a, c)
         loss = d1.mean() + d2.mean()  # chamfer as the callers form it (dip/train.py:84)
         loss.backward()
@@ -834,7 +829,9 @@ def run_b200_arm(args, w):
             "config_detail": {"pairs_per_step": pairs, "l2": "256 MB buffer rewritten between timed steps (L2 flush)",
                               "parallelism": "xyz1 rows sharded over ranks (symmetric scan: each rank evaluates its rows x "
                                              "all columns once); NCCL broadcast of both clouds, int64 MIN all_reduce of "
-                                             "the column keys, all_gather of dist1/idx1, SUM all_reduce of gradients"
+                                             "the column keys, all_gather of dist1/idx1, SUM all_reduce of gradients; "
+                                             "e2e: every rank uploads the inputs from its own pinned host copy (no "
+                                             "broadcast), rank 0 downloads the gradients and the loss"
                                              if world > 1 else "single GPU"},
             "roofline": roof,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
