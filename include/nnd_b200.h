@@ -103,7 +103,7 @@ int nnd_forward_kind(int b, int n, int m);
  * the previous one (negative: query only); default 4096, environment NND_B200_SMALL_MAX, hard maximum 16384. */
 int nnd_small_max_points(void);
 int nnd_set_small_max_points(int points);
-/* Tuning / test knob of the single-launch forward: warps per CTA (4, 8, 16), queries per lane (1, 2) and how many
+/* Tuning / test knob of the single-launch forward: warps per CTA (2, 4, 8, 16), queries per lane (1, 2, 4, 8) and how many
  * warps share one set of queries while splitting the target cloud between them (a divisor of warps).  (0, 0, 0)
  * restores the default (chosen from the problem size).  Results are bit-identical for every setting. */
 int nnd_set_small_config(int warps, int qpt, int tsplit);

@@ -1214,12 +1214,14 @@ int small_forward_impl(const float* c0, int n0, const float* c1, int n1, int b, 
     cudaEventRecord(ev[0], st);
     cudaEventRecord(ev[1], st);
   }
-  if (cfg.warps == 4 && cfg.qpt == 1) rc = launch_small_t<4, 1>(sp, (int)grid, smem, st);
-  else if (cfg.warps == 4) rc = launch_small_t<4, 2>(sp, (int)grid, smem, st);
-  else if (cfg.warps == 8 && cfg.qpt == 1) rc = launch_small_t<8, 1>(sp, (int)grid, smem, st);
-  else if (cfg.warps == 8) rc = launch_small_t<8, 2>(sp, (int)grid, smem, st);
-  else if (cfg.qpt == 1) rc = launch_small_t<16, 1>(sp, (int)grid, smem, st);
-  else rc = launch_small_t<16, 2>(sp, (int)grid, smem, st);
+#define NND_SMALL_CASE(W, Q) \
+  if (cfg.warps == W && cfg.qpt == Q) rc = launch_small_t<W, Q>(sp, (int)grid, smem, st); else
+  NND_SMALL_CASE(2, 1) NND_SMALL_CASE(2, 2) NND_SMALL_CASE(2, 4) NND_SMALL_CASE(2, 8)
+  NND_SMALL_CASE(4, 1) NND_SMALL_CASE(4, 2) NND_SMALL_CASE(4, 4) NND_SMALL_CASE(4, 8)
+  NND_SMALL_CASE(8, 1) NND_SMALL_CASE(8, 2) NND_SMALL_CASE(8, 4) NND_SMALL_CASE(8, 8)
+  NND_SMALL_CASE(16, 1) NND_SMALL_CASE(16, 2) NND_SMALL_CASE(16, 4) NND_SMALL_CASE(16, 8)
+  rc = NND_EINVAL;
+#undef NND_SMALL_CASE
   if (rc) return rc;
   ++g_launches;
   if (ev) {
@@ -1334,7 +1336,8 @@ int nnd_set_small_config(int warps, int qpt, int tsplit) {
     g_small_cfg.store(0);
     return 0;
   }
-  if (!(warps == 4 || warps == 8 || warps == 16) || !(qpt == 1 || qpt == 2) || tsplit < 1 || warps % tsplit != 0)
+  if (!(warps == 2 || warps == 4 || warps == 8 || warps == 16) || !(qpt == 1 || qpt == 2 || qpt == 4 || qpt == 8) ||
+      tsplit < 1 || warps % tsplit != 0)
     return NND_EINVAL;
   g_small_cfg.store(warps << 16 | qpt << 8 | tsplit);
   return 0;

@@ -97,7 +97,7 @@ def test_data_kinds(kind, b, n, m, fwd_path, cuda_lib, device):
 
 
 # ---------------------------------------------------------------- single-launch small-cloud kernels (nnd_small.cuh)
-SMALL_CONFIGS = [(w, q, t) for w in (4, 8, 16) for q in (1, 2) for t in (1, 2, 4, 8, 16) if w % t == 0]
+SMALL_CONFIGS = [(w, q, t) for w in (2, 4, 8, 16) for q in (1, 2, 4, 8) for t in (1, 2, 4, 8, 16) if w % t == 0]
 
 
 @pytest.mark.parametrize("warps,qpt,tsplit", SMALL_CONFIGS)

@@ -46,8 +46,8 @@ for small_max in (-1, 0):
 # every configuration of the single-launch forward, and a ragged batch (lengths read by the kernels)
 x1, x2 = (t.to(dev) for t in synthetic.make_pair("lattice", 3, 700, 900, 9))
 ref_small = F.nnd_forward_raw(x1, x2)
-for w in (4, 8, 16):
-    for q in (1, 2):
+for w in (2, 4, 8, 16):
+    for q in (1, 2, 4, 8):
         for t in (1, 2, 4, 8, 16):
             if w % t == 0:
                 lib.nnd_set_small_config(w, q, t)

@@ -112,10 +112,10 @@ def main():
         lib.nnd_set_small_max_points(before)
     if "configs" in what:
         print("== every forward configuration (warps, queries/lane, target split), forward only")
-        for b, n, m in SHAPES[:4]:
+        for b, n, m in SHAPES[:4] + [(32, 1024, 1024), (8, 4096, 4096)]:
             res = []
-            for w in (4, 8, 16):
-                for q in (1, 2):
+            for w in (2, 4, 8, 16):
+                for q in (1, 2, 4, 8):
                     for t in (1, 2, 4, 8, 16):
                         if w % t:
                             continue
@@ -125,7 +125,7 @@ def main():
             auto = graph_time(b, n, m, bwd=False)
             res.sort()
             print(f"B={b} N={n} M={m}: auto {auto * 1e3:.2f} us; best " +
-                  ", ".join(f"{c}: {t_ * 1e3:.2f} us" for t_, c in res[:6]), flush=True)
+                  ", ".join(f"{c}: {t_ * 1e3:.2f} us" for t_, c in res[:10]), flush=True)
     if "crossover" in what:
         print("== crossover: single-launch vs general path, B=1, N=M (forward+backward)")
         before = lib.nnd_small_max_points()
