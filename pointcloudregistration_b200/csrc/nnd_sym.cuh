@@ -236,6 +236,9 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
           const int koff = ch * C + 4 * s4;
           const uint4 H = *reinterpret_cast<const uint4*>(filt + koff);
           const unsigned h0 = H.x, h1 = H.y, h2 = H.z, h3 = H.w;
+          // (The slow path inline instead of the out-of-line call LOSES at every size -- behind the common test C2 2.68 ->
+          // 2.79 ms, C3 2.87 -> 3.00 ms; as four per-target tests without the common one C2 3.00 ms, C3 3.33 ms:
+          // profiles/r02_ab_sym_inline.txt.)
           const bool ev = (u0 <= h0) | (u1 <= h1) | (u2 <= h2) | (u3 <= h3);
           if (__any_sync(FULL, ev)) {
 #ifdef NND_SYM_COUNT
