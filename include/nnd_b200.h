@@ -133,6 +133,18 @@ int nnd_knn_backward_ragged_cuda_f32(const float *query, const float *target, co
                                      const long long *lenq, const long long *lent,
                                      float *grad_query, float *grad_target, void *stream);
 
+/* Warm start for registration loops (new; the reference recomputes from scratch every iteration,
+ * c2p-net/deformationpyramid/model/registration.py:231-261).  Same call as nnd_forward_cuda_f32 plus
+ * hint_idx2[b, m]: for every point of xyz2 a row of xyz1 that was its neighbour in the PREVIOUS iteration (typically
+ * the idx2 the last call returned; it MAY be the same buffer as idx2).  The symmetric kernels use the distance to that
+ * row, evaluated now, as the initial upper bound of the column minimum, which removes almost all of their column
+ * bookkeeping when the clouds moved little.  RESULTS DO NOT DEPEND ON THE HINT (any values are safe: out-of-range
+ * indices are ignored); NULL = nnd_forward_cuda_f32.  Small clouds and the two-pass path ignore it. */
+int nnd_forward_warm_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int m,
+                              float *dist1, float *dist2, int32_t *idx1, int32_t *idx2,
+                              const int32_t *hint_idx2,
+                              void *workspace, size_t workspace_bytes, void *stream);
+
 /* 1 when nnd_forward_cuda_f32 takes the symmetric kernel for clouds of n and m points (every distance evaluated
  * once: b*n*m evaluations per call), 0 when it takes the two-pass kernel (2*b*n*m evaluations; small clouds).
  * Results are bit-identical either way; bench.py uses this to count the work a launch executes. */

@@ -863,7 +863,7 @@ int forward_rows_swapped_impl(const float* c1, int n1, const float* c2, int n2, 
 // colkeys receives this launch's column keys; finalize_cols_impl turns (merged) column keys into dist2/idx2.
 int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, int row_lo, int row_hi, float* dist1,
                       int32_t* idx1, unsigned long long* colkeys, void* workspace, size_t workspace_bytes,
-                      cudaStream_t st) {
+                      cudaStream_t st, const int32_t* hint2 = nullptr) {
   cudaEvent_t* ev = nullptr;
   if (g_prof.enabled && g_prof.used < kProfSlots) ev = &g_prof.ev[4 * g_prof.used++];
   DeviceInfo di;
@@ -938,13 +938,14 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   const bool panels = path == kRowsPanel;
   // The panel path's filter seed in front of the persistent kernel as well (nnd_set_sym_seed_tiles; default 1 tile).
   const int sym_seed = g_sym_seed.load(std::memory_order_relaxed);
-  if (!panels && sym_seed > 0 && shape == kShapeLarge) {
+  if (!panels && (sym_seed > 0 || hint2 != nullptr) && shape == kShapeLarge) {
     const int t_first = (row_lo + kTT - 1) / kTT;
     int ns = row_hi / kTT - t_first;
     ns = ns > sym_seed ? sym_seed : ns;
-    if (ns > 0) {
+    if (ns > 0 || hint2 != nullptr) {  // with a hint (warm start) the seed runs even without a whole sample tile
       dim3 g((unsigned)((n2 + 511) / 512), (unsigned)b);
-      nnd_seed_filter_kernel<kTT><<<g, 256, 0, st>>>(c2, soa1, cdist, n2, yp.ttiles, yp.qtiles, t_first, ns, 1.0f, n2);
+      nnd_seed_filter_kernel<kTT><<<g, 256, 0, st>>>(c2, soa1, cdist, n2, yp.ttiles, yp.qtiles, t_first, ns < 0 ? 0 : ns,
+                                                     1.0f, n2, hint2, c1, n1, row_lo, row_hi);
       ++g_launches;
     }
   }
@@ -966,9 +967,10 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
       int ns = row_hi / kTT - t_first;
       const int want = nrows >= 500000 ? 4 : nrows >= 200000 ? 2 : 1;
       ns = ns > want ? want : ns;
-      if (ns > 0) {
+      if (ns > 0 || hint2 != nullptr) {
         dim3 g((unsigned)((n2 + 511) / 512), (unsigned)b);
-        nnd_seed_filter_kernel<kTT><<<g, 256, 0, st>>>(c2, soa1, cdist, n2, yp.ttiles, yp.qtiles, t_first, ns, 1.0f, n2);
+        nnd_seed_filter_kernel<kTT><<<g, 256, 0, st>>>(c2, soa1, cdist, n2, yp.ttiles, yp.qtiles, t_first, ns < 0 ? 0 : ns,
+                                                       1.0f, n2, hint2, c1, n1, row_lo, row_hi);
         ++g_launches;
       }
     }
@@ -1376,6 +1378,13 @@ static bool sizes_ok(int b, int n, int m) {
 
 int nnd_forward_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int m, float* dist1, float* dist2,
                          int32_t* idx1, int32_t* idx2, void* workspace, size_t workspace_bytes, void* stream) {
+  return nnd_forward_warm_cuda_f32(xyz1, xyz2, b, n, m, dist1, dist2, idx1, idx2, nullptr, workspace, workspace_bytes,
+                                   stream);
+}
+
+int nnd_forward_warm_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int m, float* dist1, float* dist2,
+                              int32_t* idx1, int32_t* idx2, const int32_t* hint_idx2, void* workspace,
+                              size_t workspace_bytes, void* stream) {
   g_launches = 0;
   if (!sizes_ok(b, n, m)) return NND_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
@@ -1391,7 +1400,9 @@ int nnd_forward_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int
     return twopass_impl(xyz1, n, xyz2, m, b, 2, dist1, idx1, dist2, idx2, workspace, workspace_bytes, st);
   const size_t rows_bytes = nnd_rows_workspace_bytes(b, n, m);
   unsigned long long* colkeys = (unsigned long long*)((char*)workspace + rows_bytes);
-  int rc = forward_rows_impl(xyz1, n, xyz2, m, b, 0, n, dist1, idx1, colkeys, workspace, rows_bytes, st);
+  // hint_idx2 may be idx2 itself (a loop's own previous result): it is read by the seed pass at the start and idx2 is
+  // written by the column finalize at the end, in stream order
+  int rc = forward_rows_impl(xyz1, n, xyz2, m, b, 0, n, dist1, idx1, colkeys, workspace, rows_bytes, st, hint_idx2);
   if (rc) return rc;
   return finalize_cols_impl(xyz1, n, xyz2, m, b, colkeys, dist2, idx2, st);
 }

@@ -190,7 +190,10 @@ template <int TT>
 __global__ void __launch_bounds__(256) nnd_seed_filter_kernel(const float* __restrict__ cols, const float* __restrict__ qsoa,
                                                               unsigned* __restrict__ cdist, int m, int ttiles,
                                                               int qtiles, int tile_first, int ns, float onef,
-                                                              long long col_stride) {
+                                                              long long col_stride,
+                                                              const int32_t* __restrict__ hint = nullptr,
+                                                              const float* __restrict__ rows_aos = nullptr, int n = 0,
+                                                              int row_lo = 0, int row_hi = 0) {
   __shared__ __align__(16) float rows[3 * TT];
   const int batch = blockIdx.y;
   const uint64_t one = pk2(onef, onef);
@@ -227,6 +230,24 @@ __global__ void __launch_bounds__(256) nnd_seed_filter_kernel(const float* __res
         best[k] = fmin3(best[k], b0, b1);
       }
     }
+  }
+  // Warm start (nnd_forward_warm_cuda_f32): hint[k] is a row that was column k's neighbour before (the previous
+  // iteration of a registration loop).  Its distance NOW, evaluated with the same packed sequence, is a real entry of
+  // column k, hence a valid upper bound of the column minimum -- and almost always the minimum itself, so the scan
+  // finds next to no column to improve.  Any index is safe: out-of-range hints are ignored.
+  if (hint != nullptr) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+      if (col[k] < m) {
+        const int j = __ldg(hint + (long long)batch * m + col[k]);
+        if (j >= row_lo && j < row_hi) {
+          const float* r = rows_aos + ((long long)batch * n + j) * 3;
+          const float rx = __ldg(r), ry = __ldg(r + 1), rz = __ldg(r + 2);
+          float d0, d1;
+          upk2(sqdist2(pk2(rx, rx), pk2(ry, ry), pk2(rz, rz), ncx[k], ncy[k], ncz[k], one), d0, d1);
+          best[k] = fmin3(best[k], d0, d1);
+        }
+      }
   }
 #pragma unroll
   for (int k = 0; k < 2; ++k)

@@ -62,8 +62,11 @@ class _on_device:
             self.guard.__exit__(*exc)
 
 
-def nnd_forward_raw(xyz1: torch.Tensor, xyz2: torch.Tensor):
-    """dist1[B,N], dist2[B,M] float32 and idx1[B,N], idx2[B,M] int32; no autograd."""
+def nnd_forward_raw(xyz1: torch.Tensor, xyz2: torch.Tensor, hint_idx2: torch.Tensor = None):
+    """dist1[B,N], dist2[B,M] float32 and idx1[B,N], idx2[B,M] int32; no autograd.
+    hint_idx2 (optional, int32 [B,M]): the idx2 of a previous call on nearly the same clouds (a registration loop's last
+    iteration) -- a warm start for the large-cloud kernels (include/nnd_b200.h: nnd_forward_warm_cuda_f32).  The
+    results never depend on it."""
     _check_clouds(xyz1, xyz2)
     lib = _cabi.load()
     xyz1 = xyz1.contiguous()
@@ -82,9 +85,14 @@ def nnd_forward_raw(xyz1: torch.Tensor, xyz2: torch.Tensor):
                                           dist2.data_ptr(), idx1.data_ptr(), idx2.data_ptr(), None, 0, _stream_ptr(dev))
         else:
             ws = _workspace(nbytes, dev)
-            rc = lib.nnd_forward_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), b, n, m, dist1.data_ptr(),
-                                          dist2.data_ptr(), idx1.data_ptr(), idx2.data_ptr(), ws.data_ptr(), ws.numel(),
-                                          _stream_ptr(dev))
+            hint = None
+            if hint_idx2 is not None:
+                if hint_idx2.dtype != torch.int32 or hint_idx2.shape != (b, m) or hint_idx2.device != dev:
+                    raise ValueError("hint_idx2 must be an int32 [B, M] tensor on the clouds' device")
+                hint = hint_idx2.contiguous().data_ptr()
+            rc = lib.nnd_forward_warm_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), b, n, m, dist1.data_ptr(),
+                                               dist2.data_ptr(), idx1.data_ptr(), idx2.data_ptr(), hint, ws.data_ptr(),
+                                               ws.numel(), _stream_ptr(dev))
     if rc:
         _cabi.check(rc, "nnd_forward_cuda_f32")
     return dist1, dist2, idx1, idx2

@@ -51,10 +51,12 @@ class ChamferLoop:
     def _body(self):
         lib, st = self.lib, _stream_ptr(self.device)
         b, n, m = self.b, self.n, self.m
-        rc = lib.nnd_forward_cuda_f32(self.x.data_ptr(), self.y.data_ptr(), b, n, m, self.dist1.data_ptr(),
-                                      self.dist2.data_ptr(), self.idx1.data_ptr(), self.idx2.data_ptr(),
-                                      self._ws.data_ptr(), self._ws.numel(), st)
-        _cabi.check(rc, "nnd_forward_cuda_f32")
+        # warm start: the loop's own idx2 of the previous iteration is the hint (any content is safe, results do not
+        # depend on it; the first iteration sees zeros = "try row 0")
+        rc = lib.nnd_forward_warm_cuda_f32(self.x.data_ptr(), self.y.data_ptr(), b, n, m, self.dist1.data_ptr(),
+                                           self.dist2.data_ptr(), self.idx1.data_ptr(), self.idx2.data_ptr(),
+                                           self.idx2.data_ptr(), self._ws.data_ptr(), self._ws.numel(), st)
+        _cabi.check(rc, "nnd_forward_warm_cuda_f32")
         # point_reduction = mean (divide by the cloud length), batch_reduction = mean, both directions summed
         s1, s2 = 1.0 / (max(n, 1) * max(b, 1)), 1.0 / (max(m, 1) * max(b, 1))
         rc = lib.nnd_chamfer_reduce_cuda_f32(self.dist1.data_ptr(), self.dist2.data_ptr(), b, n, m, self.trunc, s1, s2,
@@ -126,9 +128,10 @@ class _StaticChamfer(Function):
         b, n, m = st.b, st.n, st.m
         st.x.copy_(x.reshape(b, n, 3))
         sp = _stream_ptr(dev)
-        rc = lib.nnd_forward_cuda_f32(st.x.data_ptr(), st.y.data_ptr(), b, n, m, st.dist1.data_ptr(), st.dist2.data_ptr(),
-                                      st.idx1.data_ptr(), st.idx2.data_ptr(), st._ws.data_ptr(), st._ws.numel(), sp)
-        _cabi.check(rc, "nnd_forward_cuda_f32")
+        rc = lib.nnd_forward_warm_cuda_f32(st.x.data_ptr(), st.y.data_ptr(), b, n, m, st.dist1.data_ptr(),
+                                           st.dist2.data_ptr(), st.idx1.data_ptr(), st.idx2.data_ptr(),
+                                           st.idx2.data_ptr(), st._ws.data_ptr(), st._ws.numel(), sp)  # warm start
+        _cabi.check(rc, "nnd_forward_warm_cuda_f32")
         s1, s2 = 1.0 / (max(n, 1) * max(b, 1)), 1.0 / (max(m, 1) * max(b, 1))
         rc = lib.nnd_chamfer_reduce_cuda_f32(st.dist1.data_ptr(), st.dist2.data_ptr(), b, n, m, st.trunc, s1, s2,
                                              st.loss.data_ptr(), st._gd1.data_ptr(), st._gd2.data_ptr(),

@@ -761,3 +761,34 @@ def test_config3_ndp_loop_100k(cuda_lib, device):
             losses.append(loss.item())
         a = (a.detach() - 0.01 * n * g).requires_grad_(True)
     assert losses[1] < losses[0] and losses[-1] < losses[1]
+
+
+# ---------------------------------------------------------------- warm start (nnd_forward_warm_cuda_f32)
+@pytest.mark.parametrize("kind,b,n,m,panels", [("uniform", 2, 9000, 8200, False), ("lattice", 1, 20000, 30000, False),
+                                               ("clustered", 2, 9001, 10241, True), ("identical", 1, 9000, 9000, True)])
+def test_warm_start_never_changes_the_results(kind, b, n, m, panels, cuda_lib, device):
+    """hint_idx2 only seeds the column filter: whatever it holds -- the true neighbours, neighbours of a perturbed cloud,
+    zeros, garbage, out-of-range values -- all four outputs keep the oracle's bits."""
+    before = cuda_lib.nnd_set_panel_min_rows(1) if panels else None
+    small = cuda_lib.nnd_set_small_max_points(0)
+    try:
+        x1, x2 = synthetic.make_pair(kind, b, n, m, 58)
+        want = oracle.forward(x1.numpy(), x2.numpy(), threads=16)
+        a, c = x1.to(device), x2.to(device)
+        cold = F.nnd_forward_raw(a, c)
+        assert_forward_exact(tuple(t.cpu().numpy() for t in cold), want, what="cold: ")
+        moved = F.nnd_forward_raw(a + 0.01 * torch.randn_like(a), c)[3]
+        g = torch.Generator().manual_seed(3)
+        hints = {"true": cold[3], "previous iteration": moved, "zeros": torch.zeros_like(cold[3]),
+                 "random": torch.randint(0, n, (b, m), generator=g, dtype=torch.int32).to(device),
+                 "out of range": torch.randint(-5 * n, 5 * n, (b, m), generator=g, dtype=torch.int32).to(device)}
+        for name, h in hints.items():
+            got = F.nnd_forward_raw(a, c, hint_idx2=h)
+            assert_forward_exact(tuple(t.cpu().numpy() for t in got), want, what=f"hint = {name}: ")
+        aliased = cold[3].clone()  # the loop's own buffer as hint AND output is what ndp_loop does through the C ABI
+        with pytest.raises(ValueError):
+            F.nnd_forward_raw(a, c, hint_idx2=aliased.long())
+    finally:
+        cuda_lib.nnd_set_small_max_points(small)
+        if panels:
+            cuda_lib.nnd_set_panel_min_rows(before)
