@@ -204,6 +204,12 @@ long long nnd_set_panel_min_rows(long long rows);
  * nnd_forward_is_symmetric(n, m).)  The same helper decides inside nnd_forward_rows_cuda_f32.  One exception: a call
  * whose stream is being captured into a CUDA graph always takes the persistent kernel (results are bit-identical). */
 int nnd_rows_scan_kind(int b, int n, int m, int row_lo, int row_hi);
+/* Automatic hints for the column filter (cold start; csrc/nnd_hint.cuh): a hash grid of the register-side cloud gives
+ * every streamed point a nearby row, whose exact distance seeds the filter -- the same mechanism as the caller-supplied
+ * hint of nnd_forward_warm_cuda_f32, which takes precedence.  0 = off, 1 = in front of the panel scans (default), 2 = in
+ * front of the persistent symmetric kernel as well.  Results do not depend on it.  Returns the previous mode; other
+ * values only query. */
+int nnd_set_auto_hint(int mode);
 /* Tuning knob: sample tiles (512 rows each) of the column-filter seed pass run in front of the PERSISTENT symmetric kernel
  * (default 1; 0 = off; the panel scan always seeds).  Results do not depend on it.  Returns the previous value; negative
  * only queries. */

@@ -52,6 +52,7 @@ SIGNATURES = {
     "nnd_set_panel_tiles": (c_int, [c_int]),
     "nnd_rows_scan_kind": (c_int, [c_int, c_int, c_int, c_int, c_int]),
     "nnd_set_sym_seed_tiles": (c_int, [c_int]),
+    "nnd_set_auto_hint": (c_int, [c_int]),
     "nnd_forward_kind": (c_int, [c_int, c_int, c_int]),
     "nnd_small_max_points": (c_int, []),
     "nnd_set_small_max_points": (c_int, [c_int]),

@@ -423,6 +423,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
 
 #include "nnd_sym.cuh"
 #include "nnd_symc.cuh"
+#include "nnd_hint.cuh"
 
 // ----------------------------------------------------------------------------------
 // backward
@@ -560,10 +561,59 @@ inline size_t filter_bytes(int b, int m) { return align_up(colkey_count(b, m) * 
 
 // Workspace of the row-range forward: SoA copies of both clouds plus either orientation's keys and filter
 // (normal: row keys of xyz1 + filter of xyz2; role-swapped: row keys of xyz2 + column keys and filter of xyz1's range).
-inline size_t rows_need(int b, int n, int m) {
+// Scratch of the automatic hints (nnd_hint.cuh), placed behind everything else in the row-range workspace: one hint per
+// column, a hash table of 2^k >= 2 * rows cells, the bounding boxes.  Sized for either orientation.
+inline int hint_table_size(int rows) {
+  int t = 1024;
+  while (t < 2 * rows && t < (1 << 30)) t <<= 1;
+  return t;
+}
+inline size_t hint_bytes(int b, int n, int m) {
+  const int big = n > m ? n : m;
+  return align_up((size_t)b * big * sizeof(int32_t), 256) + align_up((size_t)b * hint_table_size(big) * sizeof(int), 256) +
+         256;
+}
+inline size_t rows_core_need(int b, int n, int m) {
   const size_t normal = key_bytes(b, n) + filter_bytes(b, m);
   const size_t swapped = key_bytes(b, m) + colkey_bytes(b, n) + filter_bytes(b, n);
   return soa_bytes(b, n) + soa_bytes(b, m) + (normal > swapped ? normal : swapped);
+}
+inline size_t rows_need(int b, int n, int m) { return rows_core_need(b, n, m) + hint_bytes(b, n, m); }
+
+// 0 = off, 1 = in front of the panel scans (default), 2 = in front of the persistent symmetric kernel too.
+std::atomic<int> g_auto_hint{1};
+
+// Fills `hint` ([b][m] int32, inside the workspace) with a nearby row of `rows` for every point of `cols`
+// (nnd_hint.cuh); returns the hint pointer, or nullptr when the clouds are too small to bother.
+const int32_t* make_hints(const float* rows, long long row_stride, int n, const float* cols, long long col_stride, int m,
+                          int b, char* scratch, int sms, cudaStream_t st) {
+  HintParams hp{};
+  hp.rows = rows;
+  hp.cols = cols;
+  hp.row_stride = row_stride;
+  hp.col_stride = col_stride;
+  hp.n = n;
+  hp.m = m;
+  hp.b = b;
+  const int big = n > m ? n : m;
+  hp.hint = (int32_t*)scratch;
+  scratch += align_up((size_t)b * big * sizeof(int32_t), 256);
+  hp.tsize = hint_table_size(n);
+  hp.table = (int*)scratch;
+  scratch += align_up((size_t)b * hint_table_size(big) * sizeof(int), 256);
+  hp.bbox = (unsigned*)scratch;
+  int g = (int)cbrt((double)n / 2.0);
+  hp.g = g < 1 ? 1 : g > 1024 ? 1024 : g;
+  auto blocks = [&](long long items) {
+    long long bl = (items + 255) / 256;
+    return (unsigned)(bl > 8ll * sms ? 8ll * sms : bl < 1 ? 1 : bl);
+  };
+  nnd_hint_clear_kernel<<<blocks((long long)b * hp.tsize), 256, 0, st>>>(hp);
+  nnd_hint_bbox_kernel<<<dim3(blocks(n), (unsigned)b), 256, 0, st>>>(hp);
+  nnd_hint_build_kernel<<<dim3(blocks(n), (unsigned)b), 256, 0, st>>>(hp);
+  nnd_hint_query_kernel<<<dim3(blocks(m), (unsigned)b), 256, 0, st>>>(hp);
+  g_launches += 4;
+  return hp.hint;
 }
 
 int check_last(cudaError_t e) { return e == cudaSuccess ? 0 : (int)e; }
@@ -817,9 +867,14 @@ int forward_rows_swapped_impl(const float* c1, int n1, const float* c2, int n2, 
     int ns = n2 / kTT;
     const int want = n2 >= 500000 ? 4 : n2 >= 200000 ? 2 : 1;
     ns = ns > want ? want : ns;
-    if (ns > 0) {
+    // automatic hints (nnd_hint.cuh): here the register side ("rows") is xyz2 and the columns are the range's points
+    const int32_t* hints = nullptr;
+    if (g_auto_hint.load(std::memory_order_relaxed) >= 1)
+      hints = make_hints(c2, n2, n2, sub, n1, nrows, b, (char*)workspace + rows_core_need(b, n1, n2), di.sms, st);
+    if (ns > 0 || hints != nullptr) {
       dim3 g((unsigned)((nrows + 511) / 512), (unsigned)b);
-      nnd_seed_filter_kernel<kTT><<<g, 256, 0, st>>>(sub, soaR, cdistS, nrows, tiles_of(nrows), tiles_of(n2), 0, ns, 1.0f, n1);
+      nnd_seed_filter_kernel<kTT><<<g, 256, 0, st>>>(sub, soaR, cdistS, nrows, tiles_of(nrows), tiles_of(n2), 0, ns, 1.0f, n1,
+                                                     hints, c2, n2, 0, n2);
       ++g_launches;
     }
   }
@@ -886,6 +941,7 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   unsigned long long* rkeys = (unsigned long long*)w;
   w += key_bytes(b, n1);
   unsigned* cdist = (unsigned*)w;
+  char* hint_scratch = (char*)workspace + rows_core_need(b, n1, n2);
   const int nrows = row_hi - row_lo;
 
   PrepParams pp{};
@@ -936,6 +992,11 @@ int forward_rows_impl(const float* c1, int n1, const float* c2, int n2, int b, i
   const int grid = yp.total_units < grid_full ? (int)yp.total_units : grid_full;
   const size_t smem = sizeof(SymStage<kTT>) * kStages + (size_t)si.threads * si.qpt * 8;  // ring + row bookkeeping
   const bool panels = path == kRowsPanel;
+  // Cold start: automatic hints from a hash grid of the rows (nnd_hint.cuh), unless the caller brought its own.
+  // Hints name rows of the WHOLE cloud; the seed pass ignores those outside [row_lo, row_hi).
+  const int auto_hint = g_auto_hint.load(std::memory_order_relaxed);
+  if (hint2 == nullptr && shape == kShapeLarge && (auto_hint >= 2 || (auto_hint == 1 && panels)))
+    hint2 = make_hints(c1, n1, n1, c2, n2, n2, b, hint_scratch, di.sms, st);
   // The panel path's filter seed in front of the persistent kernel as well (nnd_set_sym_seed_tiles; default 1 tile).
   const int sym_seed = g_sym_seed.load(std::memory_order_relaxed);
   if (!panels && (sym_seed > 0 || hint2 != nullptr) && shape == kShapeLarge) {
@@ -1355,6 +1416,12 @@ int nnd_rows_scan_kind(int b, int n, int m, int row_lo, int row_hi) {
   DeviceInfo di;
   const int sms = device_info(&di) == 0 ? di.sms : 148;  // callable without a device (tests, planning): B200 has 148 SMs
   return (int)rows_path(b, n, m, row_lo, row_hi, sms, false);
+}
+
+int nnd_set_auto_hint(int mode) {
+  const int before = g_auto_hint.load();
+  if (mode >= 0 && mode <= 2) g_auto_hint.store(mode);
+  return before;
 }
 
 int nnd_set_sym_seed_tiles(int tiles) {

@@ -792,3 +792,33 @@ def test_warm_start_never_changes_the_results(kind, b, n, m, panels, cuda_lib, d
         cuda_lib.nnd_set_small_max_points(small)
         if panels:
             cuda_lib.nnd_set_panel_min_rows(before)
+
+
+@pytest.mark.parametrize("kind,b,n,m", [("uniform", 1, 9000, 8200), ("clustered", 2, 9001, 10241), ("lattice", 1, 12000, 12345),
+                                        ("identical", 1, 9000, 9000), ("large", 1, 8200, 9000), ("tiny", 1, 8200, 9000)])
+def test_automatic_hints_never_change_the_results(kind, b, n, m, cuda_lib, device):
+    """The hash-grid hints (csrc/nnd_hint.cuh) only seed the column filter: off, in front of the panel scan, in front of
+    the persistent kernel -- and with non-finite points in the clouds -- the outputs keep the oracle's bits."""
+    small = cuda_lib.nnd_set_small_max_points(0)
+    keep = cuda_lib.nnd_set_auto_hint(-1)
+    try:
+        x1, x2 = synthetic.make_pair(kind, b, n, m, 59)
+        x1, x2 = x1.clone(), x2.clone()
+        if kind == "uniform":
+            x1[0, 7] = float("inf")
+            x2[0, 11, 1] = float("nan")
+            x1[0, 100] = 3e30
+        want = oracle.forward(x1.numpy(), x2.numpy(), threads=16)
+        for panels in (False, True):
+            before = cuda_lib.nnd_set_panel_min_rows(1 if panels else 1 << 40)
+            try:
+                for mode in (0, 1, 2):
+                    cuda_lib.nnd_set_auto_hint(mode)
+                    d1, d2, i1, i2 = gpu_forward(x1, x2, device)
+                    assert np.array_equal(i1, want[2]) and np.array_equal(i2, want[3]), (panels, mode)
+                    assert _same_with_nans(d1, want[0]) and _same_with_nans(d2, want[1]), (panels, mode)
+            finally:
+                cuda_lib.nnd_set_panel_min_rows(before)
+    finally:
+        cuda_lib.nnd_set_auto_hint(keep)
+        cuda_lib.nnd_set_small_max_points(small)
