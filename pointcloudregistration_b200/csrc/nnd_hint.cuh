@@ -9,10 +9,15 @@
 // of the visits of the first wave.  A bound from a row that is actually NEAR the column removes almost all of them
 // (measured with perfect hints, profiles/r02_warm_ab.txt: C4 251.2 -> 242.5 ms, 262 144 points 18.6 -> 16.9 ms).
 //
-// So, before the seed pass: hash the rows into a uniform grid (one representative row per cell, last writer wins -- any
-// row is a valid hint, the results never depend on which one), then for every column look at the 27 cells around it and
-// keep the nearest representative.  The seed pass evaluates the distance to that row with the library's exact packed
-// sequence, which makes it a true entry of the column, hence a valid bound.  O(N + M) work, ~0.2 % of the scan at 1M.
+// So, before the seed pass: hash the rows into uniform grids of kHintLevels resolutions (cell edge halving per level; one
+// representative row per cell, last writer wins -- any row is a valid hint, the results never depend on which one),
+// then for every column look at the 27 cells around it, finest level first, and keep the nearest representative of the
+// first level that has any (clustered clouds are hundreds of points per coarse cell: the fine levels find a row at
+// the local spacing; uniform clouds fall through to the coarse level).  The seed pass evaluates the distance to that
+// row with the library's exact packed sequence, which makes it a true entry of the column, hence a valid bound.
+// O(N + M) work, a few tenths of a percent of the scan at 1M.
+
+constexpr int kHintLevels = 3;
 
 struct HintParams {
   const float* rows;     // [b][row_stride][3]  the cloud held in registers by the scan ("rows")
@@ -23,7 +28,7 @@ struct HintParams {
   unsigned* bbox;        // [b][6] ordered-uint min x,y,z then max x,y,z
   int* table;            // [b][tsize] representative row per hashed cell, -1 = empty
   int tsize;             // power of two
-  int g;                 // cells per axis
+  int g;                 // cells per axis at the coarsest level (level l has g << l)
   int32_t* hint;         // [b][m] out
 };
 
@@ -90,8 +95,8 @@ __device__ __forceinline__ HintGrid hint_grid(const HintParams& p, int batch) {
 __device__ __forceinline__ int hint_cell(float v, float lo, float inv, int g) {
   return (int)fminf(fmaxf((v - lo) * inv, 0.f), (float)(g - 1));  // fmaxf / fminf drop NaNs: always a valid cell
 }
-__device__ __forceinline__ unsigned hint_hash(int ix, int iy, int iz) {
-  return (unsigned)ix * 73856093u ^ (unsigned)iy * 19349663u ^ (unsigned)iz * 83492791u;
+__device__ __forceinline__ unsigned hint_hash(int ix, int iy, int iz, int level) {
+  return (unsigned)ix * 73856093u ^ (unsigned)iy * 19349663u ^ (unsigned)iz * 83492791u ^ (unsigned)level * 2654435761u;
 }
 
 __global__ void __launch_bounds__(256) nnd_hint_build_kernel(HintParams p) {
@@ -101,9 +106,14 @@ __global__ void __launch_bounds__(256) nnd_hint_build_kernel(HintParams p) {
   int* table = p.table + (long long)batch * p.tsize;
   for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < p.n; j += gridDim.x * blockDim.x) {
     const float x = __ldg(r + 3 * (long long)j), y = __ldg(r + 3 * (long long)j + 1), z = __ldg(r + 3 * (long long)j + 2);
-    const unsigned h = hint_hash(hint_cell(x, g.lo[0], g.inv[0], p.g), hint_cell(y, g.lo[1], g.inv[1], p.g),
-                                 hint_cell(z, g.lo[2], g.inv[2], p.g));
-    table[h & (unsigned)(p.tsize - 1)] = j;  // last writer wins: any row of the cell will do
+#pragma unroll
+    for (int l = 0; l < kHintLevels; ++l) {
+      const int gl = p.g << l;
+      const float sc = (float)(1 << l);
+      const unsigned h = hint_hash(hint_cell(x, g.lo[0], g.inv[0] * sc, gl), hint_cell(y, g.lo[1], g.inv[1] * sc, gl),
+                                   hint_cell(z, g.lo[2], g.inv[2] * sc, gl), l);
+      table[h & (unsigned)(p.tsize - 1)] = j;  // last writer wins: any row of the cell will do
+    }
   }
 }
 
@@ -115,28 +125,35 @@ __global__ void __launch_bounds__(256) nnd_hint_query_kernel(HintParams p) {
   const int* table = p.table + (long long)batch * p.tsize;
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < p.m; k += gridDim.x * blockDim.x) {
     const float x = __ldg(c + 3 * (long long)k), y = __ldg(c + 3 * (long long)k + 1), z = __ldg(c + 3 * (long long)k + 2);
-    const int cx = hint_cell(x, g.lo[0], g.inv[0], p.g), cy = hint_cell(y, g.lo[1], g.inv[1], p.g),
-              cz = hint_cell(z, g.lo[2], g.inv[2], p.g);
     float best = __int_as_float(0x7f800000);
     int bj = -1;
+    for (int l = kHintLevels - 1; l >= 0 && bj < 0; --l) {  // finest level first; stop at the first level with a row nearby
+      const int gl = p.g << l;
+      const float sc = (float)(1 << l);
+      const int cx = hint_cell(x, g.lo[0], g.inv[0] * sc, gl), cy = hint_cell(y, g.lo[1], g.inv[1] * sc, gl),
+                cz = hint_cell(z, g.lo[2], g.inv[2] * sc, gl);
 #pragma unroll 1
-    for (int dz = -1; dz <= 1; ++dz)
+      for (int dz = -1; dz <= 1; ++dz)
 #pragma unroll
-      for (int dy = -1; dy <= 1; ++dy)
+        for (int dy = -1; dy <= 1; ++dy)
 #pragma unroll
-        for (int dx = -1; dx <= 1; ++dx) {
-          const int ix = cx + dx, iy = cy + dy, iz = cz + dz;
-          if (ix < 0 || iy < 0 || iz < 0 || ix >= p.g || iy >= p.g || iz >= p.g) continue;
-          const int j = table[hint_hash(ix, iy, iz) & (unsigned)(p.tsize - 1)];
-          if (j < 0) continue;
-          const float ex = __ldg(r + 3 * (long long)j) - x, ey = __ldg(r + 3 * (long long)j + 1) - y,
-                      ez = __ldg(r + 3 * (long long)j + 2) - z;
-          const float d = ex * ex + ey * ey + ez * ez;  // only ranks the candidates; the bound itself is evaluated exactly later
-          if (d < best) {
-            best = d;
-            bj = j;
+          for (int dx = -1; dx <= 1; ++dx) {
+            const int ix = cx + dx, iy = cy + dy, iz = cz + dz;
+            if (ix < 0 || iy < 0 || iz < 0 || ix >= gl || iy >= gl || iz >= gl) continue;
+            const int j = table[hint_hash(ix, iy, iz, l) & (unsigned)(p.tsize - 1)];
+            if (j < 0) continue;
+            const float ex = __ldg(r + 3 * (long long)j) - x, ey = __ldg(r + 3 * (long long)j + 1) - y,
+                        ez = __ldg(r + 3 * (long long)j + 2) - z;
+            const float d = ex * ex + ey * ey + ez * ez;  // only ranks the candidates; the bound is evaluated exactly later
+            // a hash collision can return a row of a far-away cell (which would end the search at this level with a
+            // useless bound): accept only rows within two cell edges of this level
+            const float ux = ex * g.inv[0] * sc, uy = ey * g.inv[1] * sc, uz = ez * g.inv[2] * sc;
+            if (ux * ux + uy * uy + uz * uz <= 4.0f && d < best) {
+              best = d;
+              bj = j;
+            }
           }
-        }
+    }
     p.hint[(long long)batch * p.m + k] = bj;
   }
 }

@@ -564,8 +564,8 @@ inline size_t filter_bytes(int b, int m) { return align_up(colkey_count(b, m) * 
 // Scratch of the automatic hints (nnd_hint.cuh), placed behind everything else in the row-range workspace: one hint per
 // column, a hash table of 2^k >= 2 * rows cells, the bounding boxes.  Sized for either orientation.
 inline int hint_table_size(int rows) {
-  int t = 1024;
-  while (t < 2 * rows && t < (1 << 30)) t <<= 1;
+  int t = 1024;  // kHintLevels entries per row, load factor <= 3/4
+  while (t < 4ll * rows && t < (1 << 30)) t <<= 1;
   return t;
 }
 inline size_t hint_bytes(int b, int n, int m) {

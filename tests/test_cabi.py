@@ -41,9 +41,9 @@ def test_version_and_error_strings(cuda_lib):
 def test_workspace_size_formula(cuda_lib):
     # SoA copies (12 B/point, padded to 512-point tiles) + 8 B/point keys for both clouds + 4 B/point column filter,
     # + 8 B/point for the second key array of a role-swapped row range, + the automatic-hint scratch (4 B/point of hints
-    # and a hash table of 2^21 cells for a million rows)
+    # and a hash table of 2^22 slots for a million rows)
     w = cuda_lib.nnd_workspace_bytes(1, 1_000_000, 1_000_000)
-    assert 1_000_000 * 52 + 4_000_000 + 4 * 2 ** 21 <= w <= 1_000_000 * 52 + 4_000_000 + 4 * 2 ** 21 + 64 * 1024
+    assert 1_000_000 * 52 + 4_000_000 + 4 * 2 ** 22 <= w <= 1_000_000 * 52 + 4_000_000 + 4 * 2 ** 22 + 64 * 1024
     assert cuda_lib.nnd_workspace_bytes(0, 10, 10) == 256
     # the row-range entry point keeps the column keys in a caller-owned buffer (they are all-reduced)
     assert cuda_lib.nnd_rows_workspace_bytes(1, 1_000_000, 1_000_000) + 8 * cuda_lib.nnd_colkeys_count(1, 1_000_000) <= w
