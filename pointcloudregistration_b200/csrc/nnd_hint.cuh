@@ -16,8 +16,19 @@
 // the local spacing; uniform clouds fall through to the coarse level).  The seed pass evaluates the distance to that
 // row with the library's exact packed sequence, which makes it a true entry of the column, hence a valid bound.
 // O(N + M) work, a few tenths of a percent of the scan at 1M.
+//
+// Measured (profiles/r02_hint_ab2.txt, forward): C4 uniform 251.4 -> 243.1 ms (85.5 -> 88.4 % of the FP32 issue peak),
+// 262 144 points uniform / crosscopy / lattice 18.6-18.9 -> 17.1 ms (79 -> 86 %).  No effect (and no cost) on the
+// "clustered" generator, whose two clouds have DIFFERENT cluster centres: a column lies in empty space ~0.1 away from the
+// nearest cluster of rows, no cell around it holds a row at any level, and it keeps the sample seed's bound (5 levels
+// change nothing, r02_hint_ab_l5.txt; true neighbours as hints would give 88.6 %, r02_warm_ab_clustered.txt).  In
+// front of the persistent kernel the hints cost more than they save at C2 / C3 (mode 2), so they are on for the
+// panel scans only.
 
-constexpr int kHintLevels = 3;
+#ifndef NND_HINT_LEVELS
+#define NND_HINT_LEVELS 3
+#endif
+constexpr int kHintLevels = NND_HINT_LEVELS;
 
 struct HintParams {
   const float* rows;     // [b][row_stride][3]  the cloud held in registers by the scan ("rows")

@@ -565,7 +565,7 @@ inline size_t filter_bytes(int b, int m) { return align_up(colkey_count(b, m) * 
 // column, a hash table of 2^k >= 2 * rows cells, the bounding boxes.  Sized for either orientation.
 inline int hint_table_size(int rows) {
   int t = 1024;  // kHintLevels entries per row, load factor <= 3/4
-  while (t < 4ll * rows && t < (1 << 30)) t <<= 1;
+  while (t < (long long)(kHintLevels + 1) * rows && t < (1 << 30)) t <<= 1;
   return t;
 }
 inline size_t hint_bytes(int b, int n, int m) {

@@ -27,9 +27,10 @@ def best_of(fn, reps=8):
     return min(ts)
 
 
-for name, b, n, cfg in (("C2", 32, 16384, 2), ("C3", 1, 100_000, 3), ("B=1 N=M=32768", 1, 32768, 7), ("C5-size uniform", 1, 262_144, 5),
+KIND = sys.argv[1] if len(sys.argv) > 1 else "uniform"
+for name, b, n, cfg in (("C2", 32, 16384, 2), ("C3", 1, 100_000, 3), ("B=1 N=M=32768", 1, 32768, 7), ("C5-size", 1, 262_144, 5),
                         ("C4", 1, 1_000_000, 4)):
-    x1, x2 = synthetic.make_pair("uniform", b, n, n, cfg)
+    x1, x2 = synthetic.make_pair(KIND, b, n, n, cfg)
     a, c = x1.to(dev), x2.to(dev)
     ref = F.nnd_forward_raw(a, c)
     cold = best_of(lambda: F.nnd_forward_raw(a, c), 8 if n < 500_000 else 3)
