@@ -25,8 +25,9 @@ from .functional import _stream_ptr, chamfer_reduce_workspace
 
 
 class ChamferLoop:
-    def __init__(self, b: int, n: int, m: int, device, trunc: float = 1e9, use_graph: bool = True):
+    def __init__(self, b: int, n: int, m: int, device, trunc: float = 1e9, use_graph: bool = True, warm: bool = True):
         self.b, self.n, self.m, self.trunc = b, n, m, float(trunc)
+        self.warm = bool(warm)  # hand the previous iteration's idx2 to the forward as a hint (results never depend on it)
         self.device = dev = torch.device(device)
         if dev.type != "cuda":
             raise RuntimeError("ChamferLoop needs a CUDA device: pointcloudregistration_b200 has no CPU path")
@@ -55,7 +56,8 @@ class ChamferLoop:
         # depend on it; the first iteration sees zeros = "try row 0")
         rc = lib.nnd_forward_warm_cuda_f32(self.x.data_ptr(), self.y.data_ptr(), b, n, m, self.dist1.data_ptr(),
                                            self.dist2.data_ptr(), self.idx1.data_ptr(), self.idx2.data_ptr(),
-                                           self.idx2.data_ptr(), self._ws.data_ptr(), self._ws.numel(), st)
+                                           self.idx2.data_ptr() if self.warm else None, self._ws.data_ptr(),
+                                           self._ws.numel(), st)
         _cabi.check(rc, "nnd_forward_warm_cuda_f32")
         # point_reduction = mean (divide by the cloud length), batch_reduction = mean, both directions summed
         s1, s2 = 1.0 / (max(n, 1) * max(b, 1)), 1.0 / (max(m, 1) * max(b, 1))
@@ -130,7 +132,8 @@ class _StaticChamfer(Function):
         sp = _stream_ptr(dev)
         rc = lib.nnd_forward_warm_cuda_f32(st.x.data_ptr(), st.y.data_ptr(), b, n, m, st.dist1.data_ptr(),
                                            st.dist2.data_ptr(), st.idx1.data_ptr(), st.idx2.data_ptr(),
-                                           st.idx2.data_ptr(), st._ws.data_ptr(), st._ws.numel(), sp)  # warm start
+                                           st.idx2.data_ptr() if st.warm else None, st._ws.data_ptr(), st._ws.numel(),
+                                           sp)  # warm start
         _cabi.check(rc, "nnd_forward_warm_cuda_f32")
         s1, s2 = 1.0 / (max(n, 1) * max(b, 1)), 1.0 / (max(m, 1) * max(b, 1))
         rc = lib.nnd_chamfer_reduce_cuda_f32(st.dist1.data_ptr(), st.dist2.data_ptr(), b, n, m, st.trunc, s1, s2,
