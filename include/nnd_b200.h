@@ -42,6 +42,7 @@ extern "C" {
 #define NND_EINVAL      10001  /* bad argument (negative size, null pointer, ...)   */
 #define NND_EWORKSPACE  10002  /* workspace too small or misaligned                 */
 #define NND_EDEVICE     10003  /* device is not compute capability 10.x             */
+#define NND_ETOOBIG     10004  /* beyond the built-in scratch of the no-allocation entry point */
 
 /* Library / build identification, e.g. "nnd_b200 0.1.0 sm_100a". */
 const char *nnd_version(void);
@@ -164,6 +165,24 @@ int nnd_profile_collect(float *kernel_ms, int *calls);
 int nnd_query_cuda_f32(const float *query, const float *target, int b, int nq, int nt,
                        float *dist, int32_t *idx,
                        void *workspace, size_t workspace_bytes, void *stream);
+
+/* No-allocation variant of nnd_query_cuda_f32.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and bit-exact results as nnd_query_cuda_f32, but the scratch (structure-of-
+ * arrays copies of both clouds + packed keys) lives in a static device array inside the library, and the call makes no
+ * cudaMalloc / cudaFree / allocating library call.
+ *   - limit: nnd_query_workspace_bytes(b, nq, nt) <= NND_NOALLOC_SCRATCH_BYTES (8 MiB, = nnd_query_noalloc_max_bytes();
+ *     12 B per padded-to-512 point of both clouds + 8 B per query, e.g. b * nq = b * nt = 262 144 fits exactly).
+ *     Larger problems return NND_ETOOBIG and launch nothing.  Shapes of the single-launch kernels (workspace 0) are
+ *     accepted too and do not touch the array.
+ *   - every device that loads the library holds the 8 MiB until the process exits;
+ *   - every call on a device shares the one array: calls that OVERLAP on the GPU (different streams, or a graph
+ *     replay beside an eager call) RACE -- keep them in one stream's order.  Nothing in the array has to be cleared
+ *     between calls: each call rewrites what it reads (the previous call's contents are harmless). */
+#define NND_NOALLOC_SCRATCH_BYTES (8u << 20)
+size_t nnd_query_noalloc_max_bytes(void);
+int nnd_query_noalloc_cuda_f32(const float *query, const float *target, int b, int nq, int nt,
+                               float *dist, int32_t *idx, void *stream);
 
 /* Replaces nnd_backward_cuda (my_lib_cuda.cpp:44-72) -> NmDistanceGradKernelLauncher
  * (nnd_cuda.cu:185-222).  OVERWRITES gradxyz1[b,n,3] and gradxyz2[b,m,3] (zero

@@ -40,6 +40,8 @@ SIGNATURES = {
     "nnd_profile_collect": (c_int, [c_void_p, c_void_p]),
     "nnd_query_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                     c_size_t, c_void_p]),
+    "nnd_query_noalloc_max_bytes": (c_size_t, []),
+    "nnd_query_noalloc_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "nnd_backward_cuda_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                        c_int, c_void_p, c_void_p, c_void_p]),
     "nnd_backward_term_cuda_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p,

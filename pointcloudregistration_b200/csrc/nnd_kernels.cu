@@ -1356,6 +1356,38 @@ int launch_grad(const GradParams& gp, cudaStream_t st) {
 // ----------------------------------------------------------------------------------
 // C ABI
 // ----------------------------------------------------------------------------------
+// ---- no-allocation entry point (nnd_query_noalloc_cuda_f32) ------------------------------------------------------
+// Scratch of the two-pass query in a file-scope device array instead of caller memory: every device that loads the
+// library holds these NND_NOALLOC_SCRATCH_BYTES until the process exits.  In host code `g_noalloc_scratch` is only a
+// host-side stand-in for the symbol, NOT a device address: the address a kernel may use comes from
+// cudaGetSymbolAddress, looked up once per device with that device current (noalloc_scratch() below).
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NND_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+int noalloc_scratch(void** out) {
+  static void* addr[64];
+  static std::atomic<bool> ready[64];
+  static std::mutex mu;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return NND_EINVAL;
+  if (!ready[dev].load(std::memory_order_acquire)) {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ready[dev].load(std::memory_order_relaxed)) {
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_noalloc_scratch);  // the current device's copy of the array
+      if (e != cudaSuccess) return (int)e;
+      if (p == nullptr || ((uintptr_t)p & 255u) != 0) return NND_EWORKSPACE;
+      addr[dev] = p;
+      ready[dev].store(true, std::memory_order_release);
+    }
+  }
+  *out = addr[dev];
+  return 0;
+}
+}  // namespace
+
 extern "C" {
 
 const char* nnd_version(void) { return NND_VERSION_STRING; }
@@ -1366,6 +1398,9 @@ const char* nnd_error_string(int code) {
     case NND_EINVAL: return "nnd: invalid argument";
     case NND_EWORKSPACE: return "nnd: workspace too small or not 256-byte aligned";
     case NND_EDEVICE: return "nnd: current device is not compute capability 10.x (B200)";
+    case NND_ETOOBIG:
+      return "nnd: problem needs more scratch than the built-in NND_NOALLOC_SCRATCH_BYTES of the no-allocation entry "
+             "point; use nnd_query_cuda_f32 with a caller-owned workspace";
     default: return cudaGetErrorString((cudaError_t)code);
   }
 }
@@ -1539,6 +1574,32 @@ int nnd_query_cuda_f32(const float* query, const float* target, int b, int nq, i
     return small_forward_impl(query, nq, target, nt, b, 1, nullptr, nullptr, dist, idx, nullptr, nullptr, st);
   if (!workspace) return NND_EINVAL;
   return twopass_impl(query, nq, target, nt, b, 1, dist, idx, nullptr, nullptr, workspace, workspace_bytes, st);
+}
+
+size_t nnd_query_noalloc_max_bytes(void) { return (size_t)NND_NOALLOC_SCRATCH_BYTES; }
+
+// nnd_query_cuda_f32 with the scratch in g_noalloc_scratch: no cudaMalloc / cudaFree / allocating library call on this
+// path (device attribute queries, cudaFuncSetAttribute and kernel launches only).  Nothing in the scratch has to
+// survive between calls or start at zero: nnd_prepare_kernel rewrites the SoA copies and the packed keys of every call
+// before the scan reads them, so the previous call's contents are harmless.  Calls that overlap on the GPU (two
+// streams, or a graph replay beside an eager call) share the array and race.
+int nnd_query_noalloc_cuda_f32(const float* query, const float* target, int b, int nq, int nt, float* dist,
+                               int32_t* idx, void* stream) {
+  g_launches = 0;
+  if (b < 0 || nq < 0 || nt < 0) return NND_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (b == 0 || nq == 0) return 0;
+  if (nt == 0) return zero_outputs(dist, idx, (long long)b * nq, st);
+  if (!query || !target || !dist || !idx) return NND_EINVAL;
+  if (!sizes_ok(b, nq, nt)) return NND_ETOOBIG;
+  if (use_small(b, nq, nt))  // single-launch kernel: needs no scratch at all
+    return small_forward_impl(query, nq, target, nt, b, 1, nullptr, nullptr, dist, idx, nullptr, nullptr, st);
+  const size_t need = soa_bytes(b, nq) + soa_bytes(b, nt) + key_bytes(b, nq);
+  if (need > (size_t)NND_NOALLOC_SCRATCH_BYTES) return NND_ETOOBIG;
+  void* scratch = nullptr;
+  int rc = noalloc_scratch(&scratch);
+  if (rc) return rc;
+  return twopass_impl(query, nq, target, nt, b, 1, dist, idx, nullptr, nullptr, scratch, need, st);
 }
 
 int nnd_backward_term_cuda_f32(const float* query, const float* target, const float* graddist, const int32_t* idx,
