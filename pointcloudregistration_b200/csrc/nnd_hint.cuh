@@ -18,11 +18,16 @@
 // O(N + M) work, a few tenths of a percent of the scan at 1M.
 //
 // Measured (profiles/r02_hint_ab2.txt, forward): C4 uniform 251.4 -> 243.1 ms (85.5 -> 88.4 % of the FP32 issue peak),
-// 262 144 points uniform / crosscopy / lattice 18.6-18.9 -> 17.1 ms (79 -> 86 %).  No effect (and no cost) on the
-// "clustered" generator, whose two clouds have DIFFERENT cluster centres: a column lies in empty space ~0.1 away from the
-// nearest cluster of rows, no cell around it holds a row at any level, and it keeps the sample seed's bound (5 levels
-// change nothing, r02_hint_ab_l5.txt; true neighbours as hints would give 88.6 %, r02_warm_ab_clustered.txt).  In
-// front of the persistent kernel the hints cost more than they save at C2 / C3 (mode 2), so they are on for the
+// 262 144 points uniform / crosscopy / lattice 18.6-18.9 -> 17.1 ms (79 -> 86 %).
+//
+// The "clustered" generator's two clouds have DIFFERENT cluster centres: a column lies in empty space ~0.1 away from the
+// nearest cluster of rows and no cell around it holds a row at any level (5 levels change nothing, r02_hint_ab_l5.txt).
+// Such columns take a coarse-to-fine DESCENT instead (end of nnd_hint_query_kernel): the table also holds coarser levels
+// (cells doubling per level down to <= 6 per axis); the column takes the nearest representative of all cells of the
+// coarsest one, then per finer level the nearest representative of the 27 cells around the current best row.
+// Measured (profiles/r02_hint_descent_ab.txt): C4 clustered 253.6 -> 244.5 ms (84.8 -> 87.9 %; true neighbours as hints
+// would give 88.6 %, r02_warm_ab_clustered.txt), C5 clustered 18.44 -> 17.49 ms (80.1 -> 84.4 %), everything else unchanged.
+// In front of the persistent kernel the hints cost more than they save at C2 / C3 (mode 2), so they are on for the
 // panel scans only.
 
 #ifndef NND_HINT_LEVELS
@@ -39,7 +44,8 @@ struct HintParams {
   unsigned* bbox;        // [b][6] ordered-uint min x,y,z then max x,y,z
   int* table;            // [b][tsize] representative row per hashed cell, -1 = empty
   int tsize;             // power of two
-  int g;                 // cells per axis at the coarsest level (level l has g << l)
+  int g;                 // cells per axis at level 0 (level l >= 0 has g << l, level -l has g >> l)
+  int coarse;            // coarse levels -1 .. -coarse below level 0 for the descent of far columns (0 = none)
   int32_t* hint;         // [b][m] out
 };
 
@@ -107,8 +113,13 @@ __device__ __forceinline__ int hint_cell(float v, float lo, float inv, int g) {
   return (int)fminf(fmaxf((v - lo) * inv, 0.f), (float)(g - 1));  // fmaxf / fminf drop NaNs: always a valid cell
 }
 __device__ __forceinline__ unsigned hint_hash(int ix, int iy, int iz, int level) {
-  return (unsigned)ix * 73856093u ^ (unsigned)iy * 19349663u ^ (unsigned)iz * 83492791u ^ (unsigned)level * 2654435761u;
+  return (unsigned)ix * 73856093u ^ (unsigned)iy * 19349663u ^ (unsigned)iz * 83492791u ^
+         (unsigned)(level + 16) * 2654435761u;
 }
+// cells per axis at `level` (negative: the coarse levels of the descent) and that level's scale relative to level 0
+// (exactly 2^level for level >= 0)
+__device__ __forceinline__ int hint_cells(int g, int level) { return level >= 0 ? g << level : max(g >> -level, 1); }
+__device__ __forceinline__ float hint_scale(int g, int level) { return (float)hint_cells(g, level) / (float)g; }
 
 __global__ void __launch_bounds__(256) nnd_hint_build_kernel(HintParams p) {
   const int batch = blockIdx.y;
@@ -117,10 +128,9 @@ __global__ void __launch_bounds__(256) nnd_hint_build_kernel(HintParams p) {
   int* table = p.table + (long long)batch * p.tsize;
   for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < p.n; j += gridDim.x * blockDim.x) {
     const float x = __ldg(r + 3 * (long long)j), y = __ldg(r + 3 * (long long)j + 1), z = __ldg(r + 3 * (long long)j + 2);
-#pragma unroll
-    for (int l = 0; l < kHintLevels; ++l) {
-      const int gl = p.g << l;
-      const float sc = (float)(1 << l);
+    for (int l = -p.coarse; l < kHintLevels; ++l) {
+      const int gl = hint_cells(p.g, l);
+      const float sc = hint_scale(p.g, l);
       const unsigned h = hint_hash(hint_cell(x, g.lo[0], g.inv[0] * sc, gl), hint_cell(y, g.lo[1], g.inv[1] * sc, gl),
                                    hint_cell(z, g.lo[2], g.inv[2] * sc, gl), l);
       table[h & (unsigned)(p.tsize - 1)] = j;  // last writer wins: any row of the cell will do
@@ -164,6 +174,55 @@ __global__ void __launch_bounds__(256) nnd_hint_query_kernel(HintParams p) {
               bj = j;
             }
           }
+    }
+    // Far columns (no row within two cell edges at any level: the clouds do not overlap here, e.g. clustered clouds with
+    // different centres).  Coarse-to-fine descent instead: the nearest representative of ALL cells of the coarsest level
+    // (at most 6^3), then per finer level the nearest representative of the 27 cells around the CURRENT BEST ROW's cell --
+    // each step moves at most one cell towards the column, and the cells halve, so the walk ends on the near face of
+    // the nearest cluster, at the finest level's resolution.  A colliding table entry is just another candidate row.
+    if (bj < 0 && p.coarse > 0) {
+      float px = 0.f, py = 0.f, pz = 0.f;  // position of the current best row
+      auto probe = [&](int ix, int iy, int iz, int lv) {
+        const int j = table[hint_hash(ix, iy, iz, lv) & (unsigned)(p.tsize - 1)];
+        if (j < 0) return;
+        const float rx = __ldg(r + 3 * (long long)j), ry = __ldg(r + 3 * (long long)j + 1), rz = __ldg(r + 3 * (long long)j + 2);
+        const float ex = rx - x, ey = ry - y, ez = rz - z;
+        const float d = ex * ex + ey * ey + ez * ez;
+        if (d < best) {
+          best = d;
+          bj = j;
+          px = rx;
+          py = ry;
+          pz = rz;
+        }
+      };
+      int lv = -p.coarse;
+      {
+        const int gl = hint_cells(p.g, lv);
+#pragma unroll 1
+        for (int iz = 0; iz < gl; ++iz)
+#pragma unroll 1
+          for (int iy = 0; iy < gl; ++iy)
+#pragma unroll 1
+            for (int ix = 0; ix < gl; ++ix) probe(ix, iy, iz, lv);
+      }
+#pragma unroll 1
+      for (++lv; lv < kHintLevels && bj >= 0; ++lv) {
+        const int gl = hint_cells(p.g, lv);
+        const float sc = hint_scale(p.g, lv);
+        const int cx = hint_cell(px, g.lo[0], g.inv[0] * sc, gl), cy = hint_cell(py, g.lo[1], g.inv[1] * sc, gl),
+                  cz = hint_cell(pz, g.lo[2], g.inv[2] * sc, gl);
+#pragma unroll 1
+        for (int dz = -1; dz <= 1; ++dz)
+#pragma unroll 1
+          for (int dy = -1; dy <= 1; ++dy)
+#pragma unroll
+            for (int dx = -1; dx <= 1; ++dx) {
+              const int ix = cx + dx, iy = cy + dy, iz = cz + dz;
+              if (ix < 0 || iy < 0 || iz < 0 || ix >= gl || iy >= gl || iz >= gl) continue;
+              probe(ix, iy, iz, lv);
+            }
+      }
     }
     p.hint[(long long)batch * p.m + k] = bj;
   }

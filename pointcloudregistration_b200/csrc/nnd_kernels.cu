@@ -604,6 +604,15 @@ const int32_t* make_hints(const float* rows, long long row_stride, int n, const 
   hp.bbox = (unsigned*)scratch;
   int g = (int)cbrt((double)n / 2.0);
   hp.g = g < 1 ? 1 : g > 1024 ? 1024 : g;
+  // coarse levels below level 0 for the descent of far columns: down to at most 6 cells per axis (all of them probed);
+  // NND_B200_HINT_COARSE=0 switches the descent off (A/B measurements)
+  static const int coarse_on = [] {
+    const char* e = getenv("NND_B200_HINT_COARSE");
+    return e ? atoi(e) : 1;
+  }();
+  hp.coarse = 0;
+  if (coarse_on)
+    while ((hp.g >> hp.coarse) > 6) ++hp.coarse;
   auto blocks = [&](long long items) {
     long long bl = (items + 255) / 256;
     return (unsigned)(bl > 8ll * sms ? 8ll * sms : bl < 1 ? 1 : bl);
