@@ -146,6 +146,21 @@ int nnd_forward_warm_cuda_f32(const float *xyz1, const float *xyz2, int b, int n
                               const int32_t *hint_idx2,
                               void *workspace, size_t workspace_bytes, void *stream);
 
+/* EXACT search with spatial pruning (opt-in; new design -- the reference only has the brute-force scan my_lib.cpp:3-25 /
+ * nnd_cuda.cu:8-130, which nnd_forward_cuda_f32 replaces and on which this project's metric is defined).  Same arguments
+ * and THE SAME BITS as nnd_forward_cuda_f32 on every input (dist bit-exact, lowest index on ties, the NaN / inf rules of
+ * my_lib.cpp:16), but only the pairs that can matter are evaluated: both clouds are sorted along a Morton curve, cut
+ * into tiles with bounding boxes, and a warp of 32 neighbouring queries skips every tile whose distance lower bound
+ * (shrunk to cover fp32 rounding) exceeds its current best (csrc/nnd_pruned.cuh).  The time depends on the geometry:
+ * clouds that overlap (registration inputs) run one to two orders of magnitude faster than the brute-force scan at
+ * 10^5 .. 10^6 points; degenerate inputs where every distance ties (all points identical) prune nothing and run
+ * slower than nnd_forward_cuda_f32.  `workspace` = nnd_pruned_workspace_bytes(b, n, m) of 256-byte aligned device
+ * memory (0 = b*n or b*m exceeds 2^31 - 1; also b <= 65535).  Uses cub::DeviceRadixSort for the curve order. */
+size_t nnd_pruned_workspace_bytes(int b, int n, int m);
+int nnd_forward_pruned_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int m,
+                                float *dist1, float *dist2, int32_t *idx1, int32_t *idx2,
+                                void *workspace, size_t workspace_bytes, void *stream);
+
 /* 1 when nnd_forward_cuda_f32 takes the symmetric kernel for clouds of n and m points (every distance evaluated
  * once: b*n*m evaluations per call), 0 when it takes the two-pass kernel (2*b*n*m evaluations; small clouds).
  * Results are bit-identical either way; bench.py uses this to count the work a launch executes. */

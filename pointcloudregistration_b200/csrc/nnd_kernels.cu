@@ -424,6 +424,7 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_kernel(const __grid_co
 #include "nnd_sym.cuh"
 #include "nnd_symc.cuh"
 #include "nnd_hint.cuh"
+#include "nnd_pruned.cuh"
 
 // ----------------------------------------------------------------------------------
 // backward
@@ -1365,6 +1366,115 @@ int launch_grad(const GradParams& gp, cudaStream_t st) {
 // ----------------------------------------------------------------------------------
 // C ABI
 // ----------------------------------------------------------------------------------
+// ---- exact search with spatial pruning (nnd_pruned.cuh; opt-in entry point nnd_forward_pruned_cuda_f32) ------------
+namespace {
+inline int pr_tiles(int n) { return (n + kPrTile - 1) / kPrTile; }
+inline int pr_stiles(int n) { return (pr_tiles(n) + kPrSuper - 1) / kPrSuper; }
+struct PrSizes {
+  size_t keys, pts, tbox, sbox, tcode;
+  size_t total() const { return 2 * keys + pts + tbox + sbox + tcode; }
+};
+inline PrSizes pr_sizes(int b, int n) {
+  PrSizes z;
+  z.keys = align_up((size_t)b * n * sizeof(unsigned long long), 256);
+  z.pts = align_up((size_t)b * pr_tiles(n) * kPrTile * sizeof(float4), 256);
+  z.tbox = align_up((size_t)b * pr_tiles(n) * sizeof(PrBox), 256);
+  z.sbox = align_up((size_t)b * pr_stiles(n) * sizeof(PrBox), 256);
+  z.tcode = align_up((size_t)b * pr_tiles(n) * sizeof(unsigned), 256);
+  return z;
+}
+inline size_t pr_temp_bytes(int b, int n, int m) {
+  const size_t t1 = exact_sort_temp_bytes((long long)b * n), t2 = exact_sort_temp_bytes((long long)b * m);
+  return align_up(t1 > t2 ? t1 : t2, 256) + 256;
+}
+inline size_t pr_need(int b, int n, int m) {
+  return pr_sizes(b, n).total() + pr_sizes(b, m).total() + 256 /* joint boxes */ + align_up((size_t)b * 24, 256) +
+         pr_temp_bytes(b, n, m);
+}
+
+// Sort one cloud along the curve and build its tiles; `keys_in` is scratch.  Returns the first CUDA error.
+int pr_prepare(PrCloud& c, int b, unsigned long long* keys_in, const unsigned* blo, const unsigned* bhi, int kb, int end_bit,
+               void* temp, size_t temp_bytes, int sms, cudaStream_t st) {
+  const long long count = (long long)b * c.n;
+  long long bl = ((long long)c.n + 255) / 256;
+  const unsigned blocks = (unsigned)(bl > 8ll * sms ? 8ll * sms : bl < 1 ? 1 : bl);
+  nnd_pr_code_kernel<<<dim3(blocks, (unsigned)b), 256, 0, st>>>(c.xyz, c.n, blo, bhi, kb, keys_in);
+  cudaError_t e = cub::DeviceRadixSort::SortKeys(temp, temp_bytes, (const unsigned long long*)keys_in, c.keys, (int)count,
+                                                 32, end_bit, st);
+  if (e != cudaSuccess) return (int)e;
+  nnd_pr_gather_kernel<<<dim3((unsigned)c.tiles, (unsigned)b), kPrTile, 0, st>>>(c);
+  nnd_pr_super_kernel<<<dim3((unsigned)((c.stiles + 3) / 4), (unsigned)b), 128, 0, st>>>(c);
+  g_launches += 3;  // + the library's sort passes
+  return check_last(cudaGetLastError());
+}
+
+int pruned_forward_impl(const float* xyz1, int n, const float* xyz2, int m, int b, float* dist1, int32_t* idx1,
+                        float* dist2, int32_t* idx2, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  if (((uintptr_t)workspace & 255u) != 0 || workspace_bytes < pr_need(b, n, m)) return NND_EWORKSPACE;
+  const int batch_bits = bits_for((unsigned long long)(b - 1));
+  int kb = (32 - batch_bits) / 3;
+  kb = kb > 10 ? 10 : kb;
+  if (kb < 1 || b > 65535) return NND_EINVAL;  // grid.y carries the batch
+  const int end_bit = 32 + 3 * kb + batch_bits;
+
+  char* w = (char*)workspace;
+  PrCloud c[2];
+  const float* src[2] = {xyz1, xyz2};
+  const int cnt[2] = {n, m};
+  for (int i = 0; i < 2; ++i) {
+    const PrSizes z = pr_sizes(b, cnt[i]);
+    c[i].xyz = src[i];
+    c[i].n = cnt[i];
+    c[i].tiles = pr_tiles(cnt[i]);
+    c[i].stiles = pr_stiles(cnt[i]);
+    c[i].keys = (unsigned long long*)w;
+    w += z.keys;
+    c[i].pts = (float4*)w;
+    w += z.pts;
+    c[i].tbox = (PrBox*)w;
+    w += z.tbox;
+    c[i].sbox = (PrBox*)w;
+    w += z.sbox;
+    c[i].tcode = (unsigned*)w;
+    w += z.tcode;
+  }
+  const size_t kmax = pr_sizes(b, n > m ? n : m).keys;
+  unsigned long long* keys_in = (unsigned long long*)w;  // shared by both clouds (one sorts after the other)
+  w += kmax;
+  // (the second cloud's "2 * keys" share covers the smaller cloud's unused input half: total() counts 2 per cloud)
+  unsigned* blo = (unsigned*)w;
+  unsigned* bhi = blo + (size_t)b * 3;
+  w += 256 + align_up((size_t)b * 24, 256);
+  void* temp = w;
+  const size_t temp_bytes = pr_temp_bytes(b, n, m);
+
+  cudaError_t e = cudaMemsetAsync(blo, 0xff, (size_t)b * 3 * sizeof(unsigned), st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(bhi, 0, (size_t)b * 3 * sizeof(unsigned), st);
+  if (e != cudaSuccess) return (int)e;
+  for (int i = 0; i < 2; ++i) {
+    long long bl = ((long long)cnt[i] + 255) / 256;
+    const unsigned blocks = (unsigned)(bl > 8ll * di.sms ? 8ll * di.sms : bl < 1 ? 1 : bl);
+    nnd_pr_bbox_kernel<<<dim3(blocks, (unsigned)b), 256, 0, st>>>(src[i], cnt[i], blo, bhi);
+    ++g_launches;
+  }
+  for (int i = 0; i < 2; ++i) {
+    rc = pr_prepare(c[i], b, keys_in, blo, bhi, kb, end_bit, temp, temp_bytes, di.sms, st);
+    if (rc) return rc;
+  }
+  for (int dir = 0; dir < 2; ++dir) {
+    PrSearch sp{c[dir], c[1 - dir], dir == 0 ? dist1 : dist2, dir == 0 ? idx1 : idx2};
+    const unsigned gx = (unsigned)((sp.q.n + 32 * kPrWarps - 1) / (32 * kPrWarps));
+    nnd_pr_search_kernel<<<dim3(gx, (unsigned)b), 32 * kPrWarps, 0, st>>>(sp);
+    ++g_launches;
+  }
+  debug_sync("pruned_forward", st);
+  return check_last(cudaGetLastError());
+}
+}  // namespace
+
 // ---- no-allocation entry point (nnd_query_noalloc_cuda_f32) ------------------------------------------------------
 // Scratch of the two-pass query in a file-scope device array instead of caller memory: every device that loads the
 // library holds these NND_NOALLOC_SCRATCH_BYTES until the process exits.  In host code `g_noalloc_scratch` is only a
@@ -1516,6 +1626,25 @@ int nnd_forward_warm_cuda_f32(const float* xyz1, const float* xyz2, int b, int n
   int rc = forward_rows_impl(xyz1, n, xyz2, m, b, 0, n, dist1, idx1, colkeys, workspace, rows_bytes, st, hint_idx2);
   if (rc) return rc;
   return finalize_cols_impl(xyz1, n, xyz2, m, b, colkeys, dist2, idx2, st);
+}
+
+size_t nnd_pruned_workspace_bytes(int b, int n, int m) {
+  if (b <= 0 || n <= 0 || m <= 0) return 256;
+  if ((long long)b * n > 0x7fffffffLL || (long long)b * m > 0x7fffffffLL) return 0;
+  return pr_need(b, n, m);
+}
+
+int nnd_forward_pruned_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int m, float* dist1, float* dist2,
+                                int32_t* idx1, int32_t* idx2, void* workspace, size_t workspace_bytes, void* stream) {
+  g_launches = 0;
+  if (!sizes_ok(b, n, m)) return NND_EINVAL;
+  if ((long long)b * n > 0x7fffffffLL || (long long)b * m > 0x7fffffffLL) return NND_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (b == 0 || (n == 0 && m == 0)) return 0;
+  if (n == 0) return zero_outputs(dist2, idx2, (long long)b * m, st);  // my_lib.cpp:9-10,21-22 with an empty inner loop
+  if (m == 0) return zero_outputs(dist1, idx1, (long long)b * n, st);
+  if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2 || !workspace) return NND_EINVAL;
+  return pruned_forward_impl(xyz1, n, xyz2, m, b, dist1, idx1, dist2, idx2, workspace, workspace_bytes, st);
 }
 
 int nnd_forward_rows_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int m, int row_lo, int row_hi,

@@ -62,12 +62,61 @@ class _on_device:
             self.guard.__exit__(*exc)
 
 
+_search_mode = "brute"  # the reference's algorithm and this project's metric; "pruned" is opt-in
+#: below this many points per cloud the pruned search's fixed cost (two sorts, tile boxes) is not worth it
+PRUNED_MIN_POINTS = 8192
+
+
+def set_search_mode(mode: str) -> str:
+    """'brute' (default): every forward evaluates all pairs (the reference's algorithm, my_lib.cpp:3-25).
+    'pruned': forwards of clouds with at least PRUNED_MIN_POINTS points each take nnd_forward_pruned_cuda_f32 --
+    the same bits (dist, idx, ties, NaN rules), one to two orders of magnitude faster on overlapping clouds.
+    Returns the previous mode."""
+    global _search_mode
+    if mode not in ("brute", "pruned"):
+        raise ValueError("search mode must be 'brute' or 'pruned'")
+    before, _search_mode = _search_mode, mode
+    return before
+
+
+def search_mode() -> str:
+    return _search_mode
+
+
+def nnd_forward_pruned_raw(xyz1: torch.Tensor, xyz2: torch.Tensor):
+    """dist1, dist2, idx1, idx2 like nnd_forward_raw, bit-identical, through the exact pruned search
+    (include/nnd_b200.h: nnd_forward_pruned_cuda_f32; csrc/nnd_pruned.cuh)."""
+    _check_clouds(xyz1, xyz2)
+    lib = _cabi.load()
+    xyz1 = xyz1.contiguous()
+    xyz2 = xyz2.contiguous()
+    b, n, _ = xyz1.shape
+    m = xyz2.size(1)
+    dev = xyz1.device
+    dist1 = torch.empty(b, n, dtype=torch.float32, device=dev)
+    dist2 = torch.empty(b, m, dtype=torch.float32, device=dev)
+    idx1 = torch.empty(b, n, dtype=torch.int32, device=dev)
+    idx2 = torch.empty(b, m, dtype=torch.int32, device=dev)
+    with _on_device(dev):
+        nbytes = lib.nnd_pruned_workspace_bytes(b, n, m)
+        if nbytes == 0:
+            raise ValueError("nnd_forward_pruned: b*n and b*m must stay below 2^31")
+        ws = _workspace(nbytes, dev)
+        rc = lib.nnd_forward_pruned_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), b, n, m, dist1.data_ptr(), dist2.data_ptr(),
+                                             idx1.data_ptr(), idx2.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+    if rc:
+        _cabi.check(rc, "nnd_forward_pruned_cuda_f32")
+    return dist1, dist2, idx1, idx2
+
+
 def nnd_forward_raw(xyz1: torch.Tensor, xyz2: torch.Tensor, hint_idx2: torch.Tensor = None):
     """dist1[B,N], dist2[B,M] float32 and idx1[B,N], idx2[B,M] int32; no autograd.
     hint_idx2 (optional, int32 [B,M]): the idx2 of a previous call on nearly the same clouds (a registration loop's last
     iteration) -- a warm start for the large-cloud kernels (include/nnd_b200.h: nnd_forward_warm_cuda_f32).  The
     results never depend on it."""
     _check_clouds(xyz1, xyz2)
+    if _search_mode == "pruned" and min(xyz1.size(1), xyz2.size(1)) >= PRUNED_MIN_POINTS and xyz1.size(0) <= 65535:
+        return nnd_forward_pruned_raw(xyz1, xyz2)
     lib = _cabi.load()
     xyz1 = xyz1.contiguous()
     xyz2 = xyz2.contiguous()

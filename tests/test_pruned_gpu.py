@@ -1,0 +1,140 @@
+"""GPU parity tests of the exact pruned search (nnd_forward_pruned_cuda_f32, csrc/nnd_pruned.cuh): it must return the
+SAME BITS as the brute-force scan of the reference (my_lib.cpp:3-25) -- dist bit-exact, lowest index on ties, the
+NaN / inf rules of my_lib.cpp:16 -- on every kind of cloud.  Checked against the CPU oracle at sizes it finishes in
+seconds and against the compiled reference's full-size digests (tests/golden/digests_full.json) at C5 / C4."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from _util import FULL_DIGESTS, assert_forward_exact, sha
+from pointcloudregistration_b200 import functional as F
+from pointcloudregistration_b200 import synthetic
+
+pytestmark = pytest.mark.gpu
+
+
+def pruned(x1, x2, device):
+    out = F.nnd_forward_pruned_raw(torch.as_tensor(x1).to(device), torch.as_tensor(x2).to(device))
+    torch.cuda.synchronize()
+    return tuple(t.cpu().numpy() for t in out)
+
+
+def _same_with_nans(got, want):
+    gn, wn = np.isnan(got), np.isnan(want)
+    return np.array_equal(gn, wn) and got[~gn].tobytes() == want[~wn].tobytes()
+
+
+@pytest.mark.parametrize("kind", synthetic.KINDS)
+@pytest.mark.parametrize("b,n,m", [(2, 3000, 2500), (1, 20000, 17001), (3, 65, 700)])
+def test_pruned_matches_the_oracle(kind, b, n, m, cuda_lib, device):
+    if kind == "identical":
+        m = n
+    x1, x2 = synthetic.make_pair(kind, b, n, m, 7)
+    got = pruned(x1, x2, device)
+    want = oracle.forward(x1.numpy(), x2.numpy(), threads=8)
+    assert_forward_exact(got, want, what=f"pruned {kind} {b}x{n}x{m}: ")
+
+
+@pytest.mark.parametrize("b,n,m", [(1, 1, 1), (2, 1, 300), (2, 300, 1), (1, 5, 70), (4, 64, 64), (1, 63, 65), (1, 2049, 33)])
+def test_pruned_tiny_and_ragged_tile_shapes(b, n, m, cuda_lib, device):
+    x1, x2 = synthetic.make_pair("lattice", b, n, m, 8)  # ties everywhere
+    got = pruned(x1, x2, device)
+    assert_forward_exact(got, oracle.forward(x1.numpy(), x2.numpy()), what=f"pruned {b}x{n}x{m}: ")
+
+
+def test_pruned_empty_clouds(cuda_lib, device):
+    x1 = synthetic.uniform(2, 40, 1)
+    e = torch.zeros(2, 0, 3)
+    d1, d2, i1, i2 = pruned(x1, e, device)  # my_lib.cpp:9-10,21-22: an empty inner loop leaves dist = 0, idx = 0
+    assert d1.shape == (2, 40) and d2.shape == (2, 0) and not d1.any() and not i1.any()
+    d1, d2, i1, i2 = pruned(e, x1, device)
+    assert d2.shape == (2, 40) and not d2.any() and not i2.any()
+
+
+@pytest.mark.parametrize("n,m", [(600, 700), (9000, 8300)])
+@pytest.mark.parametrize("first_too", [False, True])
+def test_pruned_nonfinite_inputs_follow_the_reference_rule(cuda_lib, device, n, m, first_too):
+    """my_lib.cpp:16 `if (k == 0 || d < best)`: NaN candidates are skipped unless they come first, +inf competes
+    normally -- the same inputs as test_nnd_gpu.py's brute-force test."""
+    x1 = synthetic.uniform(2, n, 11).numpy()
+    x2 = synthetic.uniform(2, m, 12).numpy()
+    x1[0, 3] = np.nan
+    x1[1, n - 1, 2] = np.inf
+    x1[1, 17] = 3e19           # squares overflow to +inf
+    x2[0, 5] = np.inf
+    x2[0, 9, 1] = np.nan
+    x2[1, m // 2] = -np.inf
+    if first_too:
+        x1[0, 0, 1] = np.nan
+        x2[1, 0] = np.inf
+        x2[0, 0, 0] = np.nan
+    d1, d2, i1, i2 = pruned(x1, x2, device)
+    w1, w2, j1, j2 = oracle.forward(x1, x2)
+    assert np.array_equal(i1, j1) and np.array_equal(i2, j2)
+    assert _same_with_nans(d1, w1) and _same_with_nans(d2, w2)
+
+
+def test_pruned_overflow_to_inf_keeps_index_zero(cuda_lib, device):
+    q = np.zeros((1, 3, 3), np.float32)
+    t = np.full((1, 40, 3), 3e19, np.float32)  # every squared distance overflows to +inf
+    d1, d2, i1, i2 = pruned(q, t, device)
+    w = oracle.forward(q, t)
+    assert np.isinf(d1).all() and (i1 == 0).all()
+    assert_forward_exact((d1, d2, i1, i2), w)
+
+
+def test_pruned_all_points_identical(cuda_lib, device):
+    """Nothing can be pruned (every bound is 0 = every best): still the lowest index everywhere."""
+    x1 = np.full((1, 3000, 3), 0.25, np.float32)
+    x2 = np.full((1, 2000, 3), 0.25, np.float32)
+    d1, d2, i1, i2 = pruned(x1, x2, device)
+    assert not d1.any() and not d2.any() and not i1.any() and not i2.any()
+
+
+def test_search_mode_switch_routes_the_public_api(cuda_lib, device):
+    import torch_nndistance as NND
+
+    x1, x2 = synthetic.make_pair("crosscopy", 2, 9000, 8500, 9)
+    a, c = x1.to(device).requires_grad_(True), x2.to(device).requires_grad_(True)
+    want = NND.nnd_with_idx(a, c)
+    before = F.set_search_mode("pruned")
+    try:
+        assert F.search_mode() == "pruned"
+        got = NND.nnd_with_idx(a, c)
+        assert cuda_lib.nnd_last_launch_count() in range(8, 12)  # 2 boxes + 2 x (code, gather, super) + 2 searches
+        (got[0].mean() + got[1].mean()).backward()
+        small = NND.nnd_with_idx(a[:, :500], c[:, :400])  # below PRUNED_MIN_POINTS: the single-launch kernels
+        assert cuda_lib.nnd_last_launch_count() == 1
+    finally:
+        F.set_search_mode(before)
+    assert F.search_mode() == "brute"
+    for g, w in zip(got, want):
+        assert torch.equal(g, w)
+    assert torch.isfinite(a.grad).all() and small[0].shape == (2, 500)
+    with pytest.raises(ValueError):
+        F.set_search_mode("fast")
+
+
+@pytest.mark.parametrize("name,kind,n,cfg", [("c5_lattice", "lattice", 262144, 5), ("c5_duplicates", "duplicates", 262144, 5),
+                                            ("c5_identical", "identical", 262144, 5), ("c5_crosscopy", "crosscopy", 262144, 5),
+                                            ("c5_clustered", "clustered", 262144, 5), ("c3_uniform", "uniform", 100_000, 3),
+                                            ("c4_uniform", "uniform", 1_000_000, 4), ("c4_clustered", "clustered", 1_000_000, 4)])
+def test_pruned_full_size_digests(name, kind, n, cfg, cuda_lib, device):
+    """WHOLE output tensors against the SHA-256 digests of the compiled reference (the same digests the brute-force path
+    is held to, tests/golden/digests_full.json)."""
+    meta = FULL_DIGESTS[name]
+    x1, x2 = synthetic.make_pair(kind, meta["b"], n, n, cfg)
+    assert sha(x1.numpy()) == meta["input_sha256"]["xyz1"] and sha(x2.numpy()) == meta["input_sha256"]["xyz2"]
+    got = pruned(x1, x2, device)
+    for k, v in zip(("dist1", "dist2", "idx1", "idx2"), got):
+        assert sha(v) == meta["sha256"][k], f"{name}: pruned {k} differs from the reference's full-size output"
+
+
+def test_pruned_c2_batch_digest(cuda_lib, device):
+    meta = FULL_DIGESTS["c2_uniform"]
+    x1, x2 = synthetic.make_pair("uniform", meta["b"], meta["n"], meta["m"], 2)
+    assert sha(x1.numpy()) == meta["input_sha256"]["xyz1"]
+    got = pruned(x1, x2, device)
+    for k, v in zip(("dist1", "dist2", "idx1", "idx2"), got):
+        assert sha(v) == meta["sha256"][k], f"c2: pruned {k} differs from the reference's full-size output"
