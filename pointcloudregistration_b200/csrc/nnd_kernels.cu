@@ -1465,7 +1465,7 @@ int pruned_forward_impl(const float* xyz1, int n, const float* xyz2, int m, int 
     if (rc) return rc;
   }
   for (int dir = 0; dir < 2; ++dir) {
-    PrSearch sp{c[dir], c[1 - dir], dir == 0 ? dist1 : dist2, dir == 0 ? idx1 : idx2};
+    PrSearch sp{c[dir], c[1 - dir], dir == 0 ? dist1 : dist2, dir == 0 ? idx1 : idx2, 1.0f};
     const unsigned gx = (unsigned)((sp.q.n + 32 * kPrWarps - 1) / (32 * kPrWarps));
     nnd_pr_search_kernel<<<dim3(gx, (unsigned)b), 32 * kPrWarps, 0, st>>>(sp);
     ++g_launches;
@@ -1752,6 +1752,15 @@ int nnd_backward_term_cuda_f32(const float* query, const float* target, const fl
   gp.t[0] = GradTerm{query, target, graddist, idx, grad_query, grad_target, nq, nt, (long long)b * nq};
   return launch_grad(gp, (cudaStream_t)stream);
 }
+
+#ifdef NND_PR_STATS
+int nnd_debug_pruned_stats(unsigned long long* out4) {  // {tiles scanned, super-tiles passed, tiles passed, warps}; resets
+  cudaError_t e = cudaMemcpyFromSymbol(out4, g_pr_stats, 4 * sizeof(unsigned long long));
+  if (e != cudaSuccess) return (int)e;
+  const unsigned long long z[4] = {0, 0, 0, 0};
+  return (int)cudaMemcpyToSymbol(g_pr_stats, z, sizeof(z));
+}
+#endif
 
 #ifdef NND_SYM_COUNT
 int nnd_debug_sym_counters(unsigned long long* out2) {  // {slow-path entries, warp steps}; resets both

@@ -24,9 +24,19 @@
 // Non-finite coordinates are safe: boxes are built with NaN-dropping min / max, every prune test is written so that a
 // NaN bound does not prune, NaN distances never win a comparison.
 
-constexpr int kPrTile = 64;    // points per tile
+#ifndef NND_PR_TILE
+#define NND_PR_TILE 64
+#endif
+constexpr int kPrTile = NND_PR_TILE;  // points per tile
 constexpr int kPrSuper = 32;   // tiles per super-tile (one lane per tile)
 constexpr int kPrWarps = 4;    // warps (of 32 queries) per CTA of the search kernel
+// A warp's 32 queries sit kPrQPL to a lane in 32 / kPrQPL lanes; the 32 / (32 / kPrQPL) = kPrQPL lane GROUPS each hold a copy
+// of the queries and take every kPrQPL-th target pair of a tile.  One broadcast LDG.128 then feeds kPrQPL evaluations per
+// lane instead of one: with one query per lane the scan was bound by the register-file return bandwidth of the loads
+// (512 bytes per warp load), 3.4 ms instead of 2.0 ms for the two searches at C4 (profiles/r02_pruned_time_v*.txt).
+constexpr int kPrQPL = 4;
+static_assert(kPrQPL == 4, "the lane mapping below is written for 4 queries per lane");
+static_assert((kPrTile / 2) % kPrQPL == 0 && kPrTile % 32 == 0, "tile size");
 
 struct PrBox {  // lo.xyz, hi.xyz (+ padding to 32 bytes)
   float lx, ly, lz, hx, hy, hz, pad0, pad1;
@@ -37,8 +47,9 @@ struct PrCloud {
   int n;                     // points per batch element
   int tiles, stiles;         // tiles / super-tiles per batch element
   unsigned long long* keys;  // [b * n] sorted keys: (batch : morton) << 32 | original index
-  float4* pts;               // [b][tiles * kPrTile]  sorted points, w = original index (int bits); padded with copies
-                             //                       of the last point carrying index INT_MAX
+  float4* pts;               // [b][tiles * kPrTile]  sorted points in PAIR layout: points 2p, 2p+1 are the two float4
+                             //   {x0, x1, y0, y1} {z0, z1, w0, w1}, w = original index (int bits) -- operands of the
+                             //   packed f32x2 sequence; padded with copies of the last point carrying index INT_MAX
   PrBox* tbox;               // [b][tiles]
   PrBox* sbox;               // [b][stiles]
   unsigned* tcode;           // [b][tiles]  high key word of the first point of the tile
@@ -135,8 +146,14 @@ __global__ void __launch_bounds__(kPrTile) nnd_pr_gather_kernel(PrCloud c) {
   const unsigned j = (unsigned)(key & 0xffffffffull);
   const float* p = c.xyz + ((long long)batch * c.n + j) * 3;
   const float x = __ldg(p), y = __ldg(p + 1), z = __ldg(p + 2);
-  c.pts[((long long)batch * c.tiles + tile) * kPrTile + threadIdx.x] =
-      make_float4(x, y, z, __int_as_float(s < c.n ? (int)j : 0x7fffffff));
+  {
+    float* o = reinterpret_cast<float*>(c.pts + ((long long)batch * c.tiles + tile) * kPrTile + (threadIdx.x & ~1u)) +
+               (threadIdx.x & 1u);
+    o[0] = x;
+    o[2] = y;
+    o[4] = z;
+    o[6] = __int_as_float(s < c.n ? (int)j : 0x7fffffff);
+  }
   __shared__ float red[6][kPrTile / 32];
   const float INF = __int_as_float(0x7f800000);
   float v[6] = {x, y, z, x, y, z};
@@ -195,24 +212,52 @@ __device__ __forceinline__ float pr_point_box(float x, float y, float z, const P
   return pr_safe(gx * gx + gy * gy + gz * gz);
 }
 
+#ifdef NND_PR_STATS  // dev instrumentation (tools/pruned_stats.py): {tiles scanned, super-tiles passed, tiles passed, warps}
+__device__ unsigned long long g_pr_stats[4];
+#endif
+
 struct PrSearch {
   PrCloud q, t;    // queries, targets
   float* dist;     // [b][q.n]  original query order
   int32_t* idx;    // [b][q.n]
+  float one;       // 1.0f at run time (sqdist2's additions are x * 1.0 + y, like every scan of this library)
 };
 
-// All kPrTile targets of one tile against this lane's query; candidates compete on (distance, original index).
-__device__ __forceinline__ void pr_scan_tile(const float4* __restrict__ tp, float qx, float qy, float qz, float& best,
-                                             int& besti) {
-#pragma unroll 8
-  for (int k = 0; k < kPrTile; ++k) {
-    const float4 t = __ldg(tp + k);  // same address in every lane: one broadcast load
-    const float dx = __fsub_rn(t.x, qx), dy = __fsub_rn(t.y, qy), dz = __fsub_rn(t.z, qz);  // target - query, my_lib.cpp:12-14
-    const float d = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));  // :15, no FMA
-    const int ti = __float_as_int(t.w);
-    const bool better = d < best || (d == best && ti < besti);
-    best = better ? d : best;
-    besti = better ? ti : besti;
+// This lane group's share of one tile (every kPrQPL-th pair of targets) against the lane's kPrQPL queries, two targets at
+// a time with the library's packed sequence (sqdist2: target - query, (xx + yy) + zz, every operation rounded
+// separately).  Candidates compete on the 64-bit key (distance bits << 32 | original index): for the non-negative
+// distances of this op unsigned key order is (distance, index) order, NaN patterns sort above +inf and never win.
+__device__ __forceinline__ unsigned long long pr_key(float d, float w) {
+  unsigned long long k;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(k) : "f"(w), "f"(d));
+  return k;
+}
+__device__ __forceinline__ void pr_scan_tile(const float4* __restrict__ tile, int grp, const uint64_t (&nqx)[kPrQPL],
+                                             const uint64_t (&nqy)[kPrQPL], const uint64_t (&nqz)[kPrQPL], uint64_t one,
+                                             unsigned long long (&bk)[kPrQPL]) {
+  const ulonglong2* tp = reinterpret_cast<const ulonglong2*>(tile) + 2 * grp;
+#pragma unroll 4
+  for (int i = 0; i < kPrTile / 2 / kPrQPL; ++i) {
+    const ulonglong2 A = __ldg(tp + 2 * kPrQPL * i);      // {x0, x1} {y0, y1}   one address per lane group
+    const ulonglong2 B = __ldg(tp + 2 * kPrQPL * i + 1);  // {z0, z1} {w0, w1}
+    float w0, w1;
+    upk2(B.y, w0, w1);
+#pragma unroll
+    for (int q = 0; q < kPrQPL; ++q) {
+      float d0, d1;
+      upk2(sqdist2(A.x, A.y, B.x, nqx[q], nqy[q], nqz[q], one), d0, d1);
+      const unsigned long long k0 = pr_key(d0, w0), k1 = pr_key(d1, w1);
+      const unsigned long long k = k0 < k1 ? k0 : k1;
+      bk[q] = k < bk[q] ? k : bk[q];
+    }
+  }
+  // every lane group has seen a quarter of the tile: combine, so that all copies of a query agree again
+#pragma unroll
+  for (int q = 0; q < kPrQPL; ++q) {
+    unsigned long long o = __shfl_xor_sync(0xffffffffu, bk[q], 8);
+    bk[q] = o < bk[q] ? o : bk[q];
+    o = __shfl_xor_sync(0xffffffffu, bk[q], 16);
+    bk[q] = o < bk[q] ? o : bk[q];
   }
 }
 
@@ -220,20 +265,46 @@ __global__ void __launch_bounds__(32 * kPrWarps) nnd_pr_search_kernel(PrSearch p
   constexpr unsigned FULL = 0xffffffffu;
   const int batch = blockIdx.y;
   const int lane = threadIdx.x & 31;
+  const int slot = lane & 7, grp = lane >> 3;  // queries 4 * slot .. 4 * slot + 3 of the warp; lane group
   const int wq = (blockIdx.x * kPrWarps + (threadIdx.x >> 5)) * 32;  // first sorted query of this warp
   const int nq = p.q.n;
   if (wq >= nq) return;
-  const int s = wq + lane < nq ? wq + lane : nq - 1;
-  const float4 q = p.q.pts[(long long)batch * p.q.tiles * kPrTile + s];
   const float INF = __int_as_float(0x7f800000);
-  // the warp's query box (NaN coordinates dropped)
-  PrBox qb;
-  qb.lx = pr_wmin(q.x == q.x ? q.x : INF);
-  qb.ly = pr_wmin(q.y == q.y ? q.y : INF);
-  qb.lz = pr_wmin(q.z == q.z ? q.z : INF);
-  qb.hx = pr_wmax(q.x == q.x ? q.x : -INF);
-  qb.hy = pr_wmax(q.y == q.y ? q.y : -INF);
-  qb.hz = pr_wmax(q.z == q.z ? q.z : -INF);
+  const uint64_t one = pk2(p.one, p.one);
+  uint64_t nqx[kPrQPL], nqy[kPrQPL], nqz[kPrQPL];
+  unsigned long long bk[kPrQPL];
+  float mx = 0.f, my = 0.f, mz = 0.f;  // the query this lane tests boxes for and writes out: number grp of its slot
+  int mw = 0;
+  PrBox qb{INF, INF, INF, -INF, -INF, -INF, 0.f, 0.f};
+#pragma unroll
+  for (int i = 0; i < kPrQPL; ++i) {
+    const int s = wq + slot * kPrQPL + i < nq ? wq + slot * kPrQPL + i : nq - 1;  // dead slots repeat the last query
+    const float* o = reinterpret_cast<const float*>(p.q.pts + (long long)batch * p.q.tiles * kPrTile + (s & ~1)) + (s & 1);
+    const float x = o[0], y = o[2], z = o[4];
+    nqx[i] = pk2(-x, -x);
+    nqy[i] = pk2(-y, -y);
+    nqz[i] = pk2(-z, -z);
+    bk[i] = 0x7f8000007fffffffull;  // (+inf, INT_MAX)
+    if (i == grp) {
+      mx = x;
+      my = y;
+      mz = z;
+      mw = __float_as_int(o[6]);
+    }
+    // the warp's query box (NaN coordinates dropped by fminf / fmaxf)
+    qb.lx = fminf(qb.lx, x);
+    qb.ly = fminf(qb.ly, y);
+    qb.lz = fminf(qb.lz, z);
+    qb.hx = fmaxf(qb.hx, x);
+    qb.hy = fmaxf(qb.hy, y);
+    qb.hz = fmaxf(qb.hz, z);
+  }
+  qb.lx = pr_wmin(qb.lx);
+  qb.ly = pr_wmin(qb.ly);
+  qb.lz = pr_wmin(qb.lz);
+  qb.hx = pr_wmax(qb.hx);
+  qb.hy = pr_wmax(qb.hy);
+  qb.hz = pr_wmax(qb.hz);
 
   const int T = p.t.tiles, ST = p.t.stiles;
   const float4* tpts = p.t.pts + (long long)batch * T * kPrTile;
@@ -241,8 +312,12 @@ __global__ void __launch_bounds__(32 * kPrWarps) nnd_pr_search_kernel(PrSearch p
   const PrBox* sbox = p.t.sbox + (long long)batch * ST;
   const unsigned* tcode = p.t.tcode + (long long)batch * T;
 
-  float best = INF;
-  int besti = 0x7fffffff;
+  float best;  // current best distance of "my" query (its bit pattern is the high key word)
+  auto mine = [&]() {
+    const unsigned long long k = grp == 0 ? bk[0] : grp == 1 ? bk[1] : grp == 2 ? bk[2] : bk[3];
+    best = __uint_as_float((unsigned)(k >> 32));
+    return k;
+  };
   // ---- seed: the target tile at this warp's position on the curve (last tile whose first code is <= ours)
   int t0;
   {
@@ -254,15 +329,22 @@ __global__ void __launch_bounds__(32 * kPrWarps) nnd_pr_search_kernel(PrSearch p
     }
     t0 = lo;
   }
-  pr_scan_tile(tpts + (long long)t0 * kPrTile, q.x, q.y, q.z, best, besti);
+  pr_scan_tile(tpts + (long long)t0 * kPrTile, grp, nqx, nqy, nqz, one, bk);
+  mine();
+#ifdef NND_PR_STATS
+  unsigned long long n_scan = 1, n_super = 0, n_tile = 0;
+#endif
   float bmax = __uint_as_float(__reduce_max_sync(FULL, __float_as_uint(best)));  // best >= +0 or +inf: bit order = value order
 
-  // ---- super-tiles -> tiles -> per-lane test -> scan
+  // ---- super-tiles -> tiles -> per-query test -> scan
   for (int sb = 0; sb < ST; sb += 32) {
     const int st = sb + lane;
     bool pass = false;
     if (st < ST) pass = !(pr_box_box(qb, sbox[st]) > bmax);
     unsigned smask = __ballot_sync(FULL, pass);
+#ifdef NND_PR_STATS
+    n_super += __popc(smask);
+#endif
     while (smask) {
       const int sst = sb + __ffs(smask) - 1;
       smask &= smask - 1;
@@ -270,26 +352,41 @@ __global__ void __launch_bounds__(32 * kPrWarps) nnd_pr_search_kernel(PrSearch p
       bool pass2 = false;
       if (tile < T && tile != t0) pass2 = !(pr_box_box(qb, tbox[tile]) > bmax);
       unsigned tmask = __ballot_sync(FULL, pass2);
+#ifdef NND_PR_STATS
+      n_tile += __popc(tmask);
+#endif
       while (tmask) {
         const int t = sst * kPrSuper + __ffs(tmask) - 1;
         tmask &= tmask - 1;
         const PrBox bx = tbox[t];
-        if (__any_sync(FULL, !(pr_point_box(q.x, q.y, q.z, bx) > best))) {
-          pr_scan_tile(tpts + (long long)t * kPrTile, q.x, q.y, q.z, best, besti);
+        if (__any_sync(FULL, !(pr_point_box(mx, my, mz, bx) > best))) {  // every query of the warp is some lane's
+          pr_scan_tile(tpts + (long long)t * kPrTile, grp, nqx, nqy, nqz, one, bk);
+          mine();
           bmax = __uint_as_float(__reduce_max_sync(FULL, __float_as_uint(best)));
+#ifdef NND_PR_STATS
+          ++n_scan;
+#endif
         }
       }
     }
   }
-
+#ifdef NND_PR_STATS
+  if (lane == 0) {
+    atomicAdd(&g_pr_stats[0], n_scan);
+    atomicAdd(&g_pr_stats[1], n_super);
+    atomicAdd(&g_pr_stats[2], n_tile);
+    atomicAdd(&g_pr_stats[3], 1ull);
+  }
+#endif
   // ---- epilogue: my_lib.cpp:16 (k = 0 is accepted unconditionally) and the scatter to the original query order
-  if (wq + lane < nq) {
+  if (wq + slot * kPrQPL + grp < nq) {
+    const unsigned long long k = mine();
     const float* t0p = p.t.xyz + (long long)batch * p.t.n * 3;
-    const float dx = __fsub_rn(__ldg(t0p), q.x), dy = __fsub_rn(__ldg(t0p + 1), q.y), dz = __fsub_rn(__ldg(t0p + 2), q.z);
+    const float dx = __fsub_rn(__ldg(t0p), mx), dy = __fsub_rn(__ldg(t0p + 1), my), dz = __fsub_rn(__ldg(t0p + 2), mz);
     const float d0 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
     const bool first = d0 != d0 || !(best < INF);
-    const long long o = (long long)batch * nq + __float_as_int(q.w);
+    const long long o = (long long)batch * nq + mw;
     p.dist[o] = first ? d0 : best;
-    p.idx[o] = first ? 0 : besti;
+    p.idx[o] = first ? 0 : (int32_t)(unsigned)(k & 0xffffffffull);
   }
 }
