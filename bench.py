@@ -638,6 +638,65 @@ def other_config(key, kind, world, rank, dev, lib, fp32_peak, digests, flush, ba
     return rec, r
 
 
+def pruned_leg(dev, lib, fp32_peak, digests, flush, brute_ms):
+    """The opt-in exact pruned search (nnd_forward_pruned_cuda_f32, csrc/nnd_pruned.cuh) beside the brute-force step:
+    forward (pruned) + backward (the same kernel as everywhere) with the headline's protocol -- inputs resident, L2
+    flushed between steps, CUDA events -- and the forward outputs held to the SAME full-size reference digests.
+    `value` is the metric the brute-force step is quoted in (2*B*N*M nominal pairs / time): not a pipe utilisation, the
+    search evaluates only the pairs that can matter.  brute_ms: ms_per_step of the brute-force step of each case."""
+    import torch
+
+    from pointcloudregistration_b200 import functional as F
+
+    out = {}
+    for key, kind in (("c2", None), ("c3", None), ("c5", None), ("c4", "uniform"), ("c4", "clustered")):
+        w = dict(WORKLOADS[key])
+        if kind:
+            w["kind"] = kind
+        name = key if not kind or kind == WORKLOADS[key]["kind"] else f"{key}:{kind}"
+        r = Runner(w, 1, 0, dev, lib, fp32_peak, digests)
+        launches = 0
+
+        def step():
+            nonlocal launches
+            d1, d2, i1, i2 = F.nnd_forward_pruned_raw(r.x1, r.x2)
+            launches = lib.nnd_last_launch_count()
+            g1, g2 = F.nnd_backward_raw(r.x1, r.x2, r.gd1, r.gd2, i1, i2)
+            return d1, d2, i1, i2
+
+        for _ in range(3):
+            last = step()
+        torch.cuda.synchronize()
+        steps = 5
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for i in range(steps):
+            flush.fill_(i & 0xff)
+            ev[i][0].record()
+            last = step()
+            ev[i][1].record()
+        torch.cuda.synchronize()
+        ms = sum(a.elapsed_time(b_) for a, b_ in ev) / steps
+        meta = digests.get(digest_key(key, w["kind"]))
+        if meta is None:
+            fwd = "no committed digest for this case"
+        else:
+            bad = [k for k, v in zip(("dist1", "dist2", "idx1", "idx2"), last) if sha_t(v) != meta["sha256"][k]]
+            fwd = "bit-exact" if not bad else "MISMATCH: " + ",".join(bad)
+        rec = {"config": config_of(w), "steps": steps, "ms_per_step": ms, "value": r.pairs / (ms * 1e-3) / 1e9,
+               "unit": UNIT, "forward": fwd, "own_kernels_per_forward": launches}
+        if brute_ms.get(name):
+            rec["brute_force_ms_per_step"] = brute_ms[name]
+            rec["speedup_vs_brute_force"] = brute_ms[name] / ms
+        out[name] = rec
+        del r, last
+        torch.cuda.empty_cache()
+    return {"api": "nnd_forward_pruned_cuda_f32 (opt-in; functional.set_search_mode('pruned')) + nnd_backward_cuda_f32",
+            "note": "exact search with spatial pruning: same bits as the brute-force scan (digest source: "
+                    "tests/golden/digests_full.json, compiled reference), only the pairs that can matter are evaluated; "
+                    "NOT the headline path -- the metric and the roofline above are defined on the brute-force scan",
+            "records": out}
+
+
 def c3_loop(r, iters=100):
     """BASELINE.json configs[2]: the repeated-chamfer loop on the C3 pair as ndp_loop.ChamferLoop runs it (forward,
     fused mean/mean epilogue, backward captured in one CUDA graph; cloud 1 follows its gradient; loss read every 10th
@@ -681,6 +740,10 @@ def gpu_baseline_leg(names):
         return json.loads(p.stdout.strip().splitlines()[-1])
     except Exception as exc:  # noqa: BLE001
         return {"unavailable": f"{type(exc).__name__}: {str(exc)[:200]}"}
+
+
+def head_name_of(workload, w):
+    return workload if w["kind"] == WORKLOADS[workload]["kind"] else f"{workload}:{w['kind']}"
 
 
 def run_b200_arm(args, w):
@@ -773,6 +836,13 @@ def run_b200_arm(args, w):
             del rr
             torch.cuda.empty_cache()
 
+    # ---- the opt-in exact pruned search beside the brute-force steps (N=1, default workload only)
+    pruned = None
+    if world == 1 and not args.no_other_configs and args.workload == "c4":
+        brute_ms = {k: v["ms_per_step"] for k, v in others.items()}
+        brute_ms[head_name_of(args.workload, w)] = total_ms / steps
+        pruned = pruned_leg(dev, lib, fp32_peak, digests, flush, brute_ms)
+
     # ---- baselines beside it (N=1 only): the reference's CPU code on the host cores, its CUDA kernels on this GPU
     cpu_base = gpu_base = None
     head_name = args.workload if w["kind"] == WORKLOADS[args.workload]["kind"] else f"{args.workload}:{w['kind']}"
@@ -844,6 +914,8 @@ def run_b200_arm(args, w):
         }
         if others:
             line["other_configs"] = others
+        if pruned is not None:
+            line["pruned_search"] = pruned
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
         if gpu_base is not None:

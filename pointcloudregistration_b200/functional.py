@@ -63,13 +63,17 @@ class _on_device:
 
 
 _search_mode = "brute"  # the reference's algorithm and this project's metric; "pruned" is opt-in
-#: below this many points per cloud the pruned search's fixed cost (two sorts, tile boxes) is not worth it
-PRUNED_MIN_POINTS = 8192
+#: below this many points per cloud / this many distance evaluations per call the pruned search's fixed cost (two
+#: sorts, tile boxes: ~0.3 ms) is not worth it -- measured crossover, profiles/r02_pruned_time_v3.txt: a lone 16 384-point
+#: pair 0.16 ms brute-force against 0.32 ms pruned, C2 (32 x 16 384) 2.68 against 0.95 ms, C3 (100 k) 2.87 against 0.67 ms
+PRUNED_MIN_POINTS = 2048
+PRUNED_MIN_EVALS = 2_000_000_000
 
 
 def set_search_mode(mode: str) -> str:
     """'brute' (default): every forward evaluates all pairs (the reference's algorithm, my_lib.cpp:3-25).
-    'pruned': forwards of clouds with at least PRUNED_MIN_POINTS points each take nnd_forward_pruned_cuda_f32 --
+    'pruned': forwards of at least PRUNED_MIN_EVALS distance evaluations (clouds of at least PRUNED_MIN_POINTS points) take
+    nnd_forward_pruned_cuda_f32 --
     the same bits (dist, idx, ties, NaN rules), one to two orders of magnitude faster on overlapping clouds.
     Returns the previous mode."""
     global _search_mode
@@ -115,7 +119,8 @@ def nnd_forward_raw(xyz1: torch.Tensor, xyz2: torch.Tensor, hint_idx2: torch.Ten
     iteration) -- a warm start for the large-cloud kernels (include/nnd_b200.h: nnd_forward_warm_cuda_f32).  The
     results never depend on it."""
     _check_clouds(xyz1, xyz2)
-    if _search_mode == "pruned" and min(xyz1.size(1), xyz2.size(1)) >= PRUNED_MIN_POINTS and xyz1.size(0) <= 65535:
+    if (_search_mode == "pruned" and min(xyz1.size(1), xyz2.size(1)) >= PRUNED_MIN_POINTS and xyz1.size(0) <= 65535
+            and xyz1.size(0) * xyz1.size(1) * xyz2.size(1) >= PRUNED_MIN_EVALS):
         return nnd_forward_pruned_raw(xyz1, xyz2)
     lib = _cabi.load()
     xyz1 = xyz1.contiguous()

@@ -66,6 +66,17 @@ def test_workspace_size_formula(cuda_lib):
     assert cuda_lib.nnd_set_small_config(0, 0, 0) == 0
 
 
+def test_pruned_search_workspace_and_validation_need_no_gpu(cuda_lib):
+    # per cloud: two 8-byte key arrays + 16-byte sorted points (padded to 64-point tiles) + boxes; plus the sort's scratch
+    w = cuda_lib.nnd_pruned_workspace_bytes(1, 1_000_000, 1_000_000)
+    assert 2 * 1_000_000 * 32 <= w <= 2 * 1_000_000 * 32 + 32 * 1024 * 1024
+    assert cuda_lib.nnd_pruned_workspace_bytes(0, 5, 5) == 256
+    assert cuda_lib.nnd_pruned_workspace_bytes(70000, 40000, 10) == 0  # b * n beyond 2^31 - 1
+    assert cuda_lib.nnd_forward_pruned_cuda_f32(None, None, -1, 1, 1, None, None, None, None, None, 0, None) == 10001
+    assert cuda_lib.nnd_forward_pruned_cuda_f32(None, None, 0, 4, 4, None, None, None, None, None, 0, None) == 0
+    assert cuda_lib.nnd_forward_pruned_cuda_f32(None, None, 1, 4, 4, None, None, None, None, None, 0, None) == 10001
+
+
 def test_argument_validation_needs_no_gpu(cuda_lib):
     # negative sizes are rejected before any CUDA call
     assert cuda_lib.nnd_forward_cuda_f32(None, None, -1, 1, 1, None, None, None, None, None, 0, None) == 10001

@@ -43,6 +43,22 @@ def test_pruned_tiny_and_ragged_tile_shapes(b, n, m, cuda_lib, device):
     assert_forward_exact(got, oracle.forward(x1.numpy(), x2.numpy()), what=f"pruned {b}x{n}x{m}: ")
 
 
+def test_pruned_random_shapes_on_coarse_grids(cuda_lib, device):
+    """Random shapes, coordinates on coarse grids of random pitch (exact ties and duplicates everywhere, the lowest
+    ORIGINAL index must win although the search visits targets in curve order), random offsets and scales."""
+    rng = np.random.default_rng(20261105)
+    for case in range(24):
+        b = int(rng.integers(1, 4))
+        n, m = int(rng.integers(1, 3000)), int(rng.integers(1, 3000))
+        cells = int(rng.choice([2, 3, 7, 16, 64, 1000]))
+        scale = float(rng.choice([1.0, 1e-3, 37.5, 4096.0]))
+        off = rng.normal(size=3).astype(np.float32) * np.float32(scale)
+        x1 = (rng.integers(0, cells, size=(b, n, 3)).astype(np.float32) / np.float32(cells)) * np.float32(scale) + off
+        x2 = (rng.integers(0, cells, size=(b, m, 3)).astype(np.float32) / np.float32(cells)) * np.float32(scale) + off
+        got = pruned(x1, x2, device)
+        assert_forward_exact(got, oracle.forward(x1, x2), what=f"case {case} ({b}x{n}x{m}, {cells} cells, scale {scale}): ")
+
+
 def test_pruned_empty_clouds(cuda_lib, device):
     x1 = synthetic.uniform(2, 40, 1)
     e = torch.zeros(2, 0, 3)
@@ -95,7 +111,7 @@ def test_pruned_all_points_identical(cuda_lib, device):
 def test_search_mode_switch_routes_the_public_api(cuda_lib, device):
     import torch_nndistance as NND
 
-    x1, x2 = synthetic.make_pair("crosscopy", 2, 9000, 8500, 9)
+    x1, x2 = synthetic.make_pair("crosscopy", 2, 40000, 30000, 9)  # 2.4e9 evaluations: above the routing threshold
     a, c = x1.to(device).requires_grad_(True), x2.to(device).requires_grad_(True)
     want = NND.nnd_with_idx(a, c)
     before = F.set_search_mode("pruned")
@@ -104,7 +120,7 @@ def test_search_mode_switch_routes_the_public_api(cuda_lib, device):
         got = NND.nnd_with_idx(a, c)
         assert cuda_lib.nnd_last_launch_count() in range(8, 12)  # 2 boxes + 2 x (code, gather, super) + 2 searches
         (got[0].mean() + got[1].mean()).backward()
-        small = NND.nnd_with_idx(a[:, :500], c[:, :400])  # below PRUNED_MIN_POINTS: the single-launch kernels
+        small = NND.nnd_with_idx(a[:, :500], c[:, :400])  # below the thresholds: the single-launch kernels
         assert cuda_lib.nnd_last_launch_count() == 1
     finally:
         F.set_search_mode(before)
