@@ -160,6 +160,11 @@ size_t nnd_pruned_workspace_bytes(int b, int n, int m);
 int nnd_forward_pruned_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int m,
                                 float *dist1, float *dist2, int32_t *idx1, int32_t *idx2,
                                 void *workspace, size_t workspace_bytes, void *stream);
+/* One direction of the same search (the pruned twin of nnd_query_cuda_f32): for every query point its nearest target
+ * point.  workspace = nnd_pruned_workspace_bytes(b, nq, nt). */
+int nnd_query_pruned_cuda_f32(const float *query, const float *target, int b, int nq, int nt,
+                              float *dist, int32_t *idx,
+                              void *workspace, size_t workspace_bytes, void *stream);
 
 /* 1 when nnd_forward_cuda_f32 takes the symmetric kernel for clouds of n and m points (every distance evaluated
  * once: b*n*m evaluations per call), 0 when it takes the two-pass kernel (2*b*n*m evaluations; small clouds).

@@ -31,6 +31,8 @@ SIGNATURES = {
     "nnd_pruned_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "nnd_forward_pruned_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                              c_void_p, c_void_p, c_size_t, c_void_p]),
+    "nnd_query_pruned_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                           c_size_t, c_void_p]),
     "nnd_rows_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "nnd_colkeys_count": (c_size_t, [c_int, c_int]),
     "nnd_row_group": (c_int, []),

@@ -1408,7 +1408,8 @@ int pr_prepare(PrCloud& c, int b, unsigned long long* keys_in, const unsigned* b
   return check_last(cudaGetLastError());
 }
 
-int pruned_forward_impl(const float* xyz1, int n, const float* xyz2, int m, int b, float* dist1, int32_t* idx1,
+// ndir == 2: both directions; ndir == 1: only cloud 1's points against cloud 2 (nnd_query_pruned_cuda_f32).
+int pruned_forward_impl(const float* xyz1, int n, const float* xyz2, int m, int b, int ndir, float* dist1, int32_t* idx1,
                         float* dist2, int32_t* idx2, void* workspace, size_t workspace_bytes, cudaStream_t st) {
   DeviceInfo di;
   int rc = device_info(&di);
@@ -1464,7 +1465,7 @@ int pruned_forward_impl(const float* xyz1, int n, const float* xyz2, int m, int 
     rc = pr_prepare(c[i], b, keys_in, blo, bhi, kb, end_bit, temp, temp_bytes, di.sms, st);
     if (rc) return rc;
   }
-  for (int dir = 0; dir < 2; ++dir) {
+  for (int dir = 0; dir < ndir; ++dir) {
     PrSearch sp{c[dir], c[1 - dir], dir == 0 ? dist1 : dist2, dir == 0 ? idx1 : idx2, 1.0f};
     const unsigned gx = (unsigned)((sp.q.n + 32 * kPrWarps - 1) / (32 * kPrWarps));
     nnd_pr_search_kernel<<<dim3(gx, (unsigned)b), 32 * kPrWarps, 0, st>>>(sp);
@@ -1644,7 +1645,19 @@ int nnd_forward_pruned_cuda_f32(const float* xyz1, const float* xyz2, int b, int
   if (n == 0) return zero_outputs(dist2, idx2, (long long)b * m, st);  // my_lib.cpp:9-10,21-22 with an empty inner loop
   if (m == 0) return zero_outputs(dist1, idx1, (long long)b * n, st);
   if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2 || !workspace) return NND_EINVAL;
-  return pruned_forward_impl(xyz1, n, xyz2, m, b, dist1, idx1, dist2, idx2, workspace, workspace_bytes, st);
+  return pruned_forward_impl(xyz1, n, xyz2, m, b, 2, dist1, idx1, dist2, idx2, workspace, workspace_bytes, st);
+}
+
+int nnd_query_pruned_cuda_f32(const float* query, const float* target, int b, int nq, int nt, float* dist, int32_t* idx,
+                              void* workspace, size_t workspace_bytes, void* stream) {
+  g_launches = 0;
+  if (!sizes_ok(b, nq, nt)) return NND_EINVAL;
+  if ((long long)b * nq > 0x7fffffffLL || (long long)b * nt > 0x7fffffffLL) return NND_EINVAL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (b == 0 || nq == 0) return 0;
+  if (nt == 0) return zero_outputs(dist, idx, (long long)b * nq, st);
+  if (!query || !target || !dist || !idx || !workspace) return NND_EINVAL;
+  return pruned_forward_impl(query, nq, target, nt, b, 1, dist, idx, nullptr, nullptr, workspace, workspace_bytes, st);
 }
 
 int nnd_forward_rows_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int m, int row_lo, int row_hi,

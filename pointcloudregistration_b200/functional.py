@@ -87,6 +87,11 @@ def search_mode() -> str:
     return _search_mode
 
 
+def _pruned_route(b: int, n: int, m: int) -> bool:
+    return (_search_mode == "pruned" and min(n, m) >= PRUNED_MIN_POINTS and b <= 65535
+            and b * n * m >= PRUNED_MIN_EVALS and b * max(n, m) < 2 ** 31)
+
+
 def nnd_forward_pruned_raw(xyz1: torch.Tensor, xyz2: torch.Tensor):
     """dist1, dist2, idx1, idx2 like nnd_forward_raw, bit-identical, through the exact pruned search
     (include/nnd_b200.h: nnd_forward_pruned_cuda_f32; csrc/nnd_pruned.cuh)."""
@@ -119,8 +124,7 @@ def nnd_forward_raw(xyz1: torch.Tensor, xyz2: torch.Tensor, hint_idx2: torch.Ten
     iteration) -- a warm start for the large-cloud kernels (include/nnd_b200.h: nnd_forward_warm_cuda_f32).  The
     results never depend on it."""
     _check_clouds(xyz1, xyz2)
-    if (_search_mode == "pruned" and min(xyz1.size(1), xyz2.size(1)) >= PRUNED_MIN_POINTS and xyz1.size(0) <= 65535
-            and xyz1.size(0) * xyz1.size(1) * xyz2.size(1) >= PRUNED_MIN_EVALS):
+    if _pruned_route(xyz1.size(0), xyz1.size(1), xyz2.size(1)):
         return nnd_forward_pruned_raw(xyz1, xyz2)
     lib = _cabi.load()
     xyz1 = xyz1.contiguous()
@@ -312,6 +316,13 @@ def nnd_query_raw(query: torch.Tensor, target: torch.Tensor):
     dev = query.device
     dist = torch.empty(b, nq, dtype=torch.float32, device=dev)
     idx = torch.empty(b, nq, dtype=torch.int32, device=dev)
+    if _pruned_route(b, nq, nt) and 0 < (pbytes := lib.nnd_pruned_workspace_bytes(b, nq, nt)):
+        with _on_device(dev):  # the exact pruned search, one direction (set_search_mode("pruned")): same bits
+            ws = _workspace(pbytes, dev)
+            rc = lib.nnd_query_pruned_cuda_f32(query.data_ptr(), target.data_ptr(), b, nq, nt, dist.data_ptr(),
+                                               idx.data_ptr(), ws.data_ptr(), ws.numel(), _stream_ptr(dev))
+        _cabi.check(rc, "nnd_query_pruned_cuda_f32")
+        return dist, idx
     with _on_device(dev):
         nbytes = lib.nnd_query_workspace_bytes(b, nq, nt)
         ws = _workspace(nbytes, dev) if nbytes else None

@@ -21,11 +21,14 @@ import torch
 from torch.autograd import Function
 
 from . import _cabi
-from .functional import _stream_ptr, chamfer_reduce_workspace
+from .functional import _pruned_route, _stream_ptr, chamfer_reduce_workspace
 
 
 class ChamferLoop:
-    def __init__(self, b: int, n: int, m: int, device, trunc: float = 1e9, use_graph: bool = True, warm: bool = True):
+    def __init__(self, b: int, n: int, m: int, device, trunc: float = 1e9, use_graph: bool = True, warm: bool = True,
+                 search: str = None):
+        """search: 'brute' (the reference's scan), 'pruned' (the exact pruned search, same bits -- DESIGN.md 4.7), or
+        None = functional.search_mode() with its size thresholds."""
         self.b, self.n, self.m, self.trunc = b, n, m, float(trunc)
         self.warm = bool(warm)  # hand the previous iteration's idx2 to the forward as a hint (results never depend on it)
         self.device = dev = torch.device(device)
@@ -41,7 +44,13 @@ class ChamferLoop:
         self.dist1, self.dist2 = torch.zeros(b, n, **f32), torch.zeros(b, m, **f32)
         self.idx1, self.idx2 = torch.zeros(b, n, **i32), torch.zeros(b, m, **i32)
         self._gd1, self._gd2 = torch.zeros(b, n, **f32), torch.zeros(b, m, **f32)
-        self._ws = torch.empty(max(self.lib.nnd_workspace_bytes(b, n, m), 256), dtype=torch.uint8, device=dev)
+        if search not in (None, "brute", "pruned"):
+            raise ValueError("search must be None, 'brute' or 'pruned'")
+        self.pruned = search == "pruned" or (search is None and _pruned_route(b, n, m))
+        nbytes = self.lib.nnd_pruned_workspace_bytes(b, n, m) if self.pruned else self.lib.nnd_workspace_bytes(b, n, m)
+        if self.pruned and (nbytes == 0 or b > 65535):
+            raise ValueError("the pruned search needs b <= 65535 and b*n, b*m < 2^31")
+        self._ws = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=dev)
         self._rws = chamfer_reduce_workspace(dev)
         self.graph = None
         self.use_graph = use_graph
@@ -54,11 +63,7 @@ class ChamferLoop:
         b, n, m = self.b, self.n, self.m
         # warm start: the loop's own idx2 of the previous iteration is the hint (any content is safe, results do not
         # depend on it; the first iteration sees zeros = "try row 0")
-        rc = lib.nnd_forward_warm_cuda_f32(self.x.data_ptr(), self.y.data_ptr(), b, n, m, self.dist1.data_ptr(),
-                                           self.dist2.data_ptr(), self.idx1.data_ptr(), self.idx2.data_ptr(),
-                                           self.idx2.data_ptr() if self.warm else None, self._ws.data_ptr(),
-                                           self._ws.numel(), st)
-        _cabi.check(rc, "nnd_forward_warm_cuda_f32")
+        self._forward(st)
         # point_reduction = mean (divide by the cloud length), batch_reduction = mean, both directions summed
         s1, s2 = 1.0 / (max(n, 1) * max(b, 1)), 1.0 / (max(m, 1) * max(b, 1))
         rc = lib.nnd_chamfer_reduce_cuda_f32(self.dist1.data_ptr(), self.dist2.data_ptr(), b, n, m, self.trunc, s1, s2,
@@ -69,6 +74,21 @@ class ChamferLoop:
                                        self.idx1.data_ptr(), self.idx2.data_ptr(), b, n, m, self.grad_x.data_ptr(),
                                        self.grad_y.data_ptr(), st)
         _cabi.check(rc, "nnd_backward_cuda_f32")
+
+    def _forward(self, st) -> None:
+        """nnd forward over the static buffers on raw stream `st` (capturable: no allocation, no host read)."""
+        lib, b, n, m = self.lib, self.b, self.n, self.m
+        if self.pruned:
+            rc = lib.nnd_forward_pruned_cuda_f32(self.x.data_ptr(), self.y.data_ptr(), b, n, m, self.dist1.data_ptr(),
+                                                 self.dist2.data_ptr(), self.idx1.data_ptr(), self.idx2.data_ptr(),
+                                                 self._ws.data_ptr(), self._ws.numel(), st)
+            _cabi.check(rc, "nnd_forward_pruned_cuda_f32")
+            return
+        rc = lib.nnd_forward_warm_cuda_f32(self.x.data_ptr(), self.y.data_ptr(), b, n, m, self.dist1.data_ptr(),
+                                           self.dist2.data_ptr(), self.idx1.data_ptr(), self.idx2.data_ptr(),
+                                           self.idx2.data_ptr() if self.warm else None, self._ws.data_ptr(),
+                                           self._ws.numel(), st)
+        _cabi.check(rc, "nnd_forward_warm_cuda_f32")
 
     def _capture(self):
         s = torch.cuda.Stream(self.device)
@@ -130,11 +150,7 @@ class _StaticChamfer(Function):
         b, n, m = st.b, st.n, st.m
         st.x.copy_(x.reshape(b, n, 3))
         sp = _stream_ptr(dev)
-        rc = lib.nnd_forward_warm_cuda_f32(st.x.data_ptr(), st.y.data_ptr(), b, n, m, st.dist1.data_ptr(),
-                                           st.dist2.data_ptr(), st.idx1.data_ptr(), st.idx2.data_ptr(),
-                                           st.idx2.data_ptr() if st.warm else None, st._ws.data_ptr(), st._ws.numel(),
-                                           sp)  # warm start
-        _cabi.check(rc, "nnd_forward_warm_cuda_f32")
+        st._forward(sp)  # warm start / pruned search as the loop was built
         s1, s2 = 1.0 / (max(n, 1) * max(b, 1)), 1.0 / (max(m, 1) * max(b, 1))
         rc = lib.nnd_chamfer_reduce_cuda_f32(st.dist1.data_ptr(), st.dist2.data_ptr(), b, n, m, st.trunc, s1, s2,
                                              st.loss.data_ptr(), st._gd1.data_ptr(), st._gd2.data_ptr(),
@@ -180,12 +196,12 @@ class GraphedIteration:
     eagerly (the comparison path of the tests).  exact=True takes the deterministic backward (bit-reproducible runs)."""
 
     def __init__(self, warp, optimizer, source: torch.Tensor, target: torch.Tensor, trunc: float = 1e9,
-                 extra_loss=None, use_graph: bool = True, exact: bool = False):
+                 extra_loss=None, use_graph: bool = True, exact: bool = False, search: str = None):
         dev = source.device
         if dev.type != "cuda":
             raise RuntimeError("GraphedIteration needs CUDA tensors: pointcloudregistration_b200 has no CPU path")
         n, m = source.shape[-2], target.shape[-2]
-        self.st = st = ChamferLoop(1, n, m, dev, trunc=trunc, use_graph=False)
+        self.st = st = ChamferLoop(1, n, m, dev, trunc=trunc, use_graph=False, search=search)
         st.exact = bool(exact)
         if st.exact:
             nbytes = st.lib.nnd_backward_exact_workspace_bytes(1, n, m)

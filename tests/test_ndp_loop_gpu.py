@@ -143,3 +143,29 @@ def test_whole_iteration_early_stop_protocol(cuda_lib, device):
     assert len(hist) == 1 and g.iterations == 1
     hist = g.run(200, read_every=20, loss_tol=0.0, break_threshold_ratio=0.0)
     assert [it for it, _ in hist] == list(range(0, 200, 20)) + [199] and hist[-1][1] < hist[0][1]
+
+
+@pytest.mark.parametrize("use_graph", [True, False])
+def test_loop_with_the_pruned_search_is_bit_identical_to_the_brute_force_loop(cuda_lib, device, use_graph):
+    """ChamferLoop(search='pruned'): the exact pruned forward (csrc/nnd_pruned.cuh, incl. the library sort) captured
+    into the CUDA graph.  Same bits out of the forward, so -- with the deterministic-order epilogue and the same
+    backward kernel on the same inputs -- the same loss bits, iteration after iteration."""
+    n, m = 30000, 26000
+    x0, y = synthetic.make_pair("crosscopy", 1, n, m, 97)
+    y = y.to(device)
+    a = ndp_loop.ChamferLoop(1, n, m, device, use_graph=use_graph, search="pruned")
+    b = ndp_loop.ChamferLoop(1, n, m, device, use_graph=use_graph, search="brute")
+    assert a.pruned and not b.pruned
+    a.set_target(y)
+    b.set_target(y)
+    xa = x0.to(device).clone()
+    for it in range(8):
+        la, ga = a.step(xa)
+        lb, gb = b.step(xa)
+        assert torch.equal(a.idx1, b.idx1) and torch.equal(a.idx2, b.idx2), it
+        assert torch.equal(a.dist1, b.dist1) and torch.equal(a.dist2, b.dist2), it
+        assert torch.equal(la, lb), (it, float(la), float(lb))
+        scale = gb.abs().max()
+        assert (ga - gb).abs().max() <= 1e-5 * scale  # atomic summation order
+        xa = xa - 5.0 * gb
+    assert a.replays == 8

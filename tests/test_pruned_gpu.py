@@ -59,6 +59,23 @@ def test_pruned_random_shapes_on_coarse_grids(cuda_lib, device):
         assert_forward_exact(got, oracle.forward(x1, x2), what=f"case {case} ({b}x{n}x{m}, {cells} cells, scale {scale}): ")
 
 
+def test_pruned_query_one_direction(cuda_lib, device):
+    """nnd_query_pruned_cuda_f32 through functional.nnd_query_raw with the search mode switched on."""
+    q, t = synthetic.make_pair("clustered", 1, 70000, 50000, 10)  # 3.5e9 evaluations: above the routing threshold
+    qd, td = q.to(device), t.to(device)
+    want = F.nnd_query_raw(qd, td)
+    brute_launches = cuda_lib.nnd_last_launch_count()
+    before = F.set_search_mode("pruned")
+    try:
+        got = F.nnd_query_raw(qd, td)
+        assert cuda_lib.nnd_last_launch_count() == 9 != brute_launches  # 2 boxes + 2 x (code, gather, super) + 1 search
+    finally:
+        F.set_search_mode(before)
+    assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
+    w = oracle.query(q.numpy()[:, :3000], t.numpy(), threads=8)
+    assert got[0].cpu().numpy()[:, :3000].tobytes() == w[0].tobytes() and got[1].cpu().numpy()[:, :3000].tobytes() == w[1].tobytes()
+
+
 def test_pruned_empty_clouds(cuda_lib, device):
     x1 = synthetic.uniform(2, 40, 1)
     e = torch.zeros(2, 0, 3)
