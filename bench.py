@@ -687,6 +687,8 @@ def pruned_leg(dev, lib, fp32_peak, digests, flush, brute_ms):
         if brute_ms.get(name):
             rec["brute_force_ms_per_step"] = brute_ms[name]
             rec["speedup_vs_brute_force"] = brute_ms[name] / ms
+        if key == "c3":  # the same 100-iteration graph loop as other_configs.c3.loop, pruned forward inside the graph
+            rec["loop"] = c3_loop(r, search="pruned")
         out[name] = rec
         del r, last
         torch.cuda.empty_cache()
@@ -697,14 +699,14 @@ def pruned_leg(dev, lib, fp32_peak, digests, flush, brute_ms):
             "records": out}
 
 
-def c3_loop(r, iters=100):
+def c3_loop(r, iters=100, search="brute"):
     """BASELINE.json configs[2]: the repeated-chamfer loop on the C3 pair as ndp_loop.ChamferLoop runs it (forward,
     fused mean/mean epilogue, backward captured in one CUDA graph; cloud 1 follows its gradient; loss read every 10th
     iteration as registration.py:250-256 needs).  ms per iteration from CUDA events around the whole loop."""
     from pointcloudregistration_b200 import ndp_loop
 
     torch = r.torch
-    loop = ndp_loop.ChamferLoop(r.b, r.n, r.m, r.dev)
+    loop = ndp_loop.ChamferLoop(r.b, r.n, r.m, r.dev, search=search)
     loop.set_target(r.x2)
     x = r.x1.clone()
     for _ in range(10):  # untimed: graph capture and upload, clocks
@@ -725,6 +727,7 @@ def c3_loop(r, iters=100):
     ms = e0.elapsed_time(e1) / iters
     return {"iterations": iters, "ms_per_iteration": ms, "value": r.pairs / (ms * 1e-3) / 1e9, "unit": UNIT,
             "loss_first": first, "loss_last": last,
+            "search": search,
             "note": "ndp_loop.ChamferLoop: forward + fused truncated-chamfer epilogue + backward replayed as one CUDA "
                     "graph, x <- x - 0.01 * d(sum)/dx between iterations, loss read every 10th iteration"}
 
