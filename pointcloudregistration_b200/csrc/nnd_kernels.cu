@@ -1631,7 +1631,7 @@ int nnd_forward_warm_cuda_f32(const float* xyz1, const float* xyz2, int b, int n
 
 size_t nnd_pruned_workspace_bytes(int b, int n, int m) {
   if (b <= 0 || n <= 0 || m <= 0) return 256;
-  if ((long long)b * n > 0x7fffffffLL || (long long)b * m > 0x7fffffffLL) return 0;
+  if ((long long)b * n > 0x7fffffffLL - 1024 || (long long)b * m > 0x7fffffffLL - 1024) return 0;
   return pr_need(b, n, m);
 }
 
@@ -1639,7 +1639,7 @@ int nnd_forward_pruned_cuda_f32(const float* xyz1, const float* xyz2, int b, int
                                 int32_t* idx1, int32_t* idx2, void* workspace, size_t workspace_bytes, void* stream) {
   g_launches = 0;
   if (!sizes_ok(b, n, m)) return NND_EINVAL;
-  if ((long long)b * n > 0x7fffffffLL || (long long)b * m > 0x7fffffffLL) return NND_EINVAL;
+  if ((long long)b * n > 0x7fffffffLL - 1024 || (long long)b * m > 0x7fffffffLL - 1024) return NND_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   if (b == 0 || (n == 0 && m == 0)) return 0;
   if (n == 0) return zero_outputs(dist2, idx2, (long long)b * m, st);  // my_lib.cpp:9-10,21-22 with an empty inner loop
@@ -1652,7 +1652,7 @@ int nnd_query_pruned_cuda_f32(const float* query, const float* target, int b, in
                               void* workspace, size_t workspace_bytes, void* stream) {
   g_launches = 0;
   if (!sizes_ok(b, nq, nt)) return NND_EINVAL;
-  if ((long long)b * nq > 0x7fffffffLL || (long long)b * nt > 0x7fffffffLL) return NND_EINVAL;
+  if ((long long)b * nq > 0x7fffffffLL - 1024 || (long long)b * nt > 0x7fffffffLL - 1024) return NND_EINVAL;
   cudaStream_t st = (cudaStream_t)stream;
   if (b == 0 || nq == 0) return 0;
   if (nt == 0) return zero_outputs(dist, idx, (long long)b * nq, st);

@@ -38,7 +38,7 @@ constexpr int kPrQPL = 4;
 static_assert(kPrQPL == 4, "the lane mapping below is written for 4 queries per lane");
 static_assert((kPrTile / 2) % kPrQPL == 0 && kPrTile % 32 == 0, "tile size");
 
-struct PrBox {  // lo.xyz, hi.xyz (+ padding to 32 bytes)
+struct __align__(32) PrBox {  // lo.xyz, hi.xyz (+ padding to 32 bytes: two 16-byte loads)
   float lx, ly, lz, hx, hy, hz, pad0, pad1;
 };
 
