@@ -7,8 +7,6 @@ owns rows [lo1_r, hi1_r) (boundaries on multiples of the kernel's row group).  B
 needed in full on every rank (12 MB per million points), so they are broadcast over NVLink.
 
     forward : broadcast(xyz1), broadcast(xyz2)            [optional: caller may already hold them]
-              (equal shards + role-swapped scan: broadcast(xyz2), scatter of the own rows of xyz1, and an in-place
-               all_gather of the other ranks' rows that travels WHILE the scan runs)
               rows kernel  -> dist1/idx1 of the own rows (final) + per-column partial keys
               all_reduce(MIN, int64) of the column keys   <- the one real exchange step (8 B / point)
               column finalize -> dist2/idx2, replicated
@@ -113,15 +111,6 @@ class CudaCompute:
         return out
 
     @staticmethod
-    def rows_read_only_own_rows(b: int, n: int, m: int, lo: int, hi: int) -> bool:
-        """True when rows() reads nothing of xyz1 outside [lo, hi): the role-swapped panel scan (scan kind 3,
-        include/nnd_b200.h) streams the own rows as columns and keeps xyz2 in registers.  sharded_forward then lets
-        the rest of xyz1 arrive WHILE the scan runs."""
-        from . import _cabi
-
-        return int(_cabi.load().nnd_rows_scan_kind(b, n, m, lo, hi)) == 3
-
-    @staticmethod
     def finalize_cols(xyz1: torch.Tensor, xyz2: torch.Tensor, colkeys: torch.Tensor):
         from .functional import nnd_finalize_cols_raw
 
@@ -216,30 +205,15 @@ def sharded_forward(xyz1, xyz2, group=None, src=None, gather=True, compute=CudaC
     cloud 2)."""
     rank, world = _world(group)
     _mark("start", xyz1)
+    if src is not None and world > 1:
+        dist.broadcast(xyz1, src=src, group=group)
+        dist.broadcast(xyz2, src=src, group=group)
+        _mark("broadcast xyz1, xyz2", xyz1)
     n, m = xyz1.size(1), xyz2.size(1)
     align = compute.row_group()
     lo1, hi1 = uniform_shard_range(n, world, rank, align)
     lo2, hi2 = shard_range(m, world, rank)
     info = ShardInfo(rank, world, lo1, hi1, lo2, hi2)
-    rest = None  # in-flight all_gather of the other ranks' rows of xyz1
-    if src is not None and world > 1:
-        stride = shard_stride(n, world, align)
-        own_only = getattr(compute, "rows_read_only_own_rows", None)
-        if (xyz1.is_cuda and xyz1.size(0) == 1 and xyz1.is_contiguous() and n == world * stride and m > 0
-                and own_only is not None and all(own_only(1, n, m, r * stride, (r + 1) * stride) for r in range(world))):
-            # The scan needs ALL of xyz2 but only this rank's rows of xyz1 (role-swapped panel scan): send those rows
-            # first and let the other ranks' rows arrive while the scan runs.  Every shard has `stride` rows, so the
-            # all_gather is in place (input = this rank's slice of the output) and never writes the rows being read.
-            dist.broadcast(xyz2, src=src, group=group)
-            flat = xyz1.view(world, stride * 3)
-            dist.scatter(flat[rank], scatter_list=[flat[r] for r in range(world)] if rank == src else None, src=src,
-                         group=group)
-            rest = dist.all_gather_into_tensor(flat.view(-1), flat[rank], group=group, async_op=True)
-            _mark("broadcast xyz2, scatter own rows of xyz1 (the other rows arrive behind the scan)", xyz1)
-        else:
-            dist.broadcast(xyz1, src=src, group=group)
-            dist.broadcast(xyz2, src=src, group=group)
-            _mark("broadcast xyz1, xyz2", xyz1)
     if xyz1.size(0) == 0 or n == 0 or m == 0:  # my_lib.cpp:9-10,21-22: empty inner loop -> zeros
         z = lambda cols: (xyz1.new_zeros(xyz1.size(0), cols), torch.zeros(xyz1.size(0), cols, dtype=torch.int32,  # noqa: E731
                                                                           device=xyz1.device))
@@ -247,9 +221,6 @@ def sharded_forward(xyz1, xyz2, group=None, src=None, gather=True, compute=CudaC
         return d1, d2, i1, i2, info
     d1, i1, colkeys = compute.rows(xyz1, xyz2, lo1, hi1)
     _mark("rows kernel (prepare + scan + finalize rows)", xyz1)
-    if rest is not None:
-        rest.wait()  # all of xyz1 is needed from here on (column finalize, backward)
-        _mark("all_gather of the other ranks' rows of xyz1: what is left of it after the scan", xyz1)
     pending = None
     if world > 1:
         # the one real exchange step first (the column finalize waits for it) ...

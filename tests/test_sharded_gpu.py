@@ -222,56 +222,3 @@ def test_two_ranks_nccl(cuda_lib, tmp_path):
         z = torch.load(f"{tmp_path}/r{r}.pt")
         assert_forward_exact(tuple(z[k].numpy() for k in ("d1", "d2", "i1", "i2")), want, what=f"rank {r}: ")
         assert_grad_close((z["g1"].numpy(), z["g2"].numpy()), wg, what=f"rank {r}: ")
-
-
-def _nccl_overlap_worker(rank, world, port, n, m, out):
-    import torch.distributed as dist
-
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-    torch.cuda.set_device(rank)
-    dev = torch.device("cuda", rank)
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
-    try:
-        from pointcloudregistration_b200 import _cabi, sharded, synthetic
-
-        _cabi.load().nnd_set_panel_min_rows(20000)  # shards of 24 000 rows against 40 003 columns: role-swapped panel scan
-        x1, x2 = synthetic.make_pair("crosscopy", 1, n, m, 72)
-        if rank != 0:
-            x1, x2 = torch.zeros_like(x1), torch.zeros_like(x2)
-        a = x1.to(dev).requires_grad_(True)
-        c = x2.to(dev).requires_grad_(True)
-        sharded.trace = []
-        d1, d2, i1, i2 = sharded.nnd_sharded_with_idx(a, c, src=0)
-        phases = [name for name, _ in sharded.trace]
-        sharded.trace = None
-        gd1, gd2 = synthetic.grad_pair(1, n, m, 72)
-        ((d1 * gd1.to(dev)).sum() + (d2 * gd2.to(dev)).sum()).backward()
-        full1 = bool(torch.equal(a.detach().cpu(), synthetic.make_pair("crosscopy", 1, n, m, 72)[0]))  # all of xyz1 arrived
-        torch.save(dict(d1=d1.detach().cpu(), d2=d2.detach().cpu(), i1=i1.cpu(), i2=i2.cpu(), g1=a.grad.cpu(), g2=c.grad.cpu(),
-                        phases=phases, full1=full1), f"{out}/r{rank}.pt")
-    finally:
-        dist.destroy_process_group()
-
-
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-def test_two_ranks_nccl_inputs_arrive_behind_the_scan(cuda_lib, tmp_path):
-    """Equal shards + role-swapped scan: xyz2 is broadcast, the own rows of xyz1 are scattered, and the other ranks'
-    rows arrive through an in-place all_gather WHILE the scan runs (sharded_forward).  Same results, bit for bit."""
-    import torch.multiprocessing as mp
-
-    import oracle
-    from _util import assert_forward_exact, assert_grad_close
-    from pointcloudregistration_b200 import synthetic
-
-    n, m = 48000, 40003
-    mp.spawn(_nccl_overlap_worker, args=(2, _free_port(), n, m, str(tmp_path)), nprocs=2, join=True)
-    x1, x2 = synthetic.make_pair("crosscopy", 1, n, m, 72)
-    gd1, gd2 = synthetic.grad_pair(1, n, m, 72)
-    want = oracle.forward(x1.numpy(), x2.numpy(), threads=16)
-    wg = oracle.backward(x1.numpy(), x2.numpy(), gd1.numpy(), gd2.numpy(), want[2], want[3])
-    for r in range(2):
-        z = torch.load(f"{tmp_path}/r{r}.pt")
-        assert any(p.startswith("broadcast xyz2, scatter own rows") for p in z["phases"]), z["phases"]
-        assert z["full1"]
-        assert_forward_exact(tuple(z[k].numpy() for k in ("d1", "d2", "i1", "i2")), want, what=f"rank {r}: ")
-        assert_grad_close((z["g1"].numpy(), z["g2"].numpy()), wg, what=f"rank {r}: ")
