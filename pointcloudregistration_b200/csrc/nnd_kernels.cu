@@ -1421,6 +1421,16 @@ inline size_t pr_need(int b, int n, int m) {
          pr_temp_bytes(b, n, m);
 }
 
+// Query groups (b * ceil(n / 32)) below which the warps of a CTA share a group (nnd_pr_search_kernel<kPrWarps>).
+// NND_B200_PR_SPLIT_BELOW overrides (0 = never share; A/B measurements).
+inline long long pr_split_below() {
+  static const long long v = [] {
+    const char* e = getenv("NND_B200_PR_SPLIT_BELOW");
+    return e ? atoll(e) : 16384ll;
+  }();
+  return v;
+}
+
 // Sort one cloud along the curve and build its tiles; `keys_in` is scratch.  Returns the first CUDA error.
 int pr_prepare(PrCloud& c, int b, unsigned long long* keys_in, const unsigned* blo, const unsigned* bhi, int kb, int end_bit,
                void* temp, size_t temp_bytes, int sms, cudaStream_t st) {
@@ -1496,8 +1506,19 @@ int pruned_forward_impl(const float* xyz1, int n, const float* xyz2, int m, int 
   }
   for (int dir = 0; dir < ndir; ++dir) {
     PrSearch sp{c[dir], c[1 - dir], dir == 0 ? dist1 : dist2, dir == 0 ? idx1 : idx2, 1.0f};
-    const unsigned gx = (unsigned)((sp.q.n + 32 * kPrWarps - 1) / (32 * kPrWarps));
-    nnd_pr_search_kernel<<<dim3(gx, (unsigned)b), 32 * kPrWarps, 0, st>>>(sp);
+    // The 4 warps of a CTA share a group of 32 queries when one warp per group would not fill the machine, and
+    // whenever the target cloud is large (many tiles per group: sharing evens out the warps' very different tile
+    // counts); small clouds in large batches keep one warp per group (a few tiles each: the shared seed tile and the
+    // repeated box tests would dominate).  Measured, profiles/r02_pruned_split_ab.txt: C3 0.67 -> 0.48 ms, C5
+    // 0.87-1.42 -> 0.74-0.88 ms, C4 2.62 / 2.86 -> 2.41 / 2.24 ms; C2 0.95 -> 1.02 ms if it shared.
+    const long long groups = ((long long)sp.q.n + 31) / 32;
+    const bool shared_groups = pr_split_below() > 0 && (groups * b < pr_split_below() || sp.t.n >= 65536);
+    if (!shared_groups) {
+      const unsigned gx = (unsigned)((groups + kPrWarps - 1) / kPrWarps);
+      nnd_pr_search_kernel<1><<<dim3(gx, (unsigned)b), 32 * kPrWarps, 0, st>>>(sp);
+    } else {
+      nnd_pr_search_kernel<kPrWarps><<<dim3((unsigned)groups, (unsigned)b), 32 * kPrWarps, 0, st>>>(sp);
+    }
     ++g_launches;
   }
   debug_sync("pruned_forward", st);

@@ -261,14 +261,34 @@ __device__ __forceinline__ void pr_scan_tile(const float4* __restrict__ tile, in
   }
 }
 
+// SPLIT == 1: every warp of the CTA owns its own group of 32 queries.  SPLIT == kPrWarps: the warps of the CTA SHARE one
+// group and each takes the target tiles t with t % SPLIT == its number -- for clouds too small to fill the machine with
+// one warp per group (C3: 3 125 groups for 592 schedulers; the search is then a chain of dependent tile visits and
+// latency-bound).  The warps publish their current best distances in shared memory (atomicMin on the bit patterns: any
+// published value is a real distance of that query, so pruning with it is as valid as pruning with the own one) and
+// merge their keys there at the end.
+template <int SPLIT>
 __global__ void __launch_bounds__(32 * kPrWarps) nnd_pr_search_kernel(PrSearch p) {
+  static_assert(SPLIT == 1 || SPLIT == kPrWarps, "one group per warp or one per CTA");
   constexpr unsigned FULL = 0xffffffffu;
   const int batch = blockIdx.y;
   const int lane = threadIdx.x & 31;
-  const int slot = lane & 7, grp = lane >> 3;  // queries 4 * slot .. 4 * slot + 3 of the warp; lane group
-  const int wq = (blockIdx.x * kPrWarps + (threadIdx.x >> 5)) * 32;  // first sorted query of this warp
+  const int slot = lane & 7, grp = lane >> 3;  // queries 4 * slot .. 4 * slot + 3 of the group; lane group
+  const int warp = threadIdx.x >> 5;
+  const int part = SPLIT == 1 ? 0 : warp;  // which share of the tiles this warp takes
+  const int wq = (SPLIT == 1 ? blockIdx.x * kPrWarps + warp : blockIdx.x) * 32;  // first sorted query of the group
   const int nq = p.q.n;
-  if (wq >= nq) return;
+  if (wq >= nq) return;  // SPLIT > 1: the whole CTA leaves together
+  __shared__ unsigned best_s[32];
+  __shared__ unsigned long long key_s[32];
+  const int qi = slot * kPrQPL + grp;  // "my" query inside the group
+  if (SPLIT > 1) {
+    if (warp == 0) {
+      best_s[lane] = 0x7f800000u;
+      key_s[lane] = 0x7f8000007fffffffull;
+    }
+    __syncthreads();
+  }
   const float INF = __int_as_float(0x7f800000);
   const uint64_t one = pk2(p.one, p.one);
   uint64_t nqx[kPrQPL], nqy[kPrQPL], nqz[kPrQPL];
@@ -329,8 +349,12 @@ __global__ void __launch_bounds__(32 * kPrWarps) nnd_pr_search_kernel(PrSearch p
     }
     t0 = lo;
   }
-  pr_scan_tile(tpts + (long long)t0 * kPrTile, grp, nqx, nqy, nqz, one, bk);
+  pr_scan_tile(tpts + (long long)t0 * kPrTile, grp, nqx, nqy, nqz, one, bk);  // (every warp of a shared group: good bounds)
   mine();
+  auto share = [&]() {  // publish my query's best distance, adopt the other warps' if lower
+    if (SPLIT > 1) best = fminf(best, __uint_as_float(atomicMin(&best_s[qi], __float_as_uint(best))));
+  };
+  share();
 #ifdef NND_PR_STATS
   unsigned long long n_scan = 1, n_super = 0, n_tile = 0;
 #endif
@@ -348,9 +372,13 @@ __global__ void __launch_bounds__(32 * kPrWarps) nnd_pr_search_kernel(PrSearch p
     while (smask) {
       const int sst = sb + __ffs(smask) - 1;
       smask &= smask - 1;
+      if (SPLIT > 1) {  // what the other warps of the group found meanwhile
+        best = fminf(best, __uint_as_float(*reinterpret_cast<volatile unsigned*>(&best_s[qi])));
+        bmax = __uint_as_float(__reduce_max_sync(FULL, __float_as_uint(best)));
+      }
       const int tile = sst * kPrSuper + lane;
       bool pass2 = false;
-      if (tile < T && tile != t0) pass2 = !(pr_box_box(qb, tbox[tile]) > bmax);
+      if (tile < T && tile != t0 && (SPLIT == 1 || tile % SPLIT == part)) pass2 = !(pr_box_box(qb, tbox[tile]) > bmax);
       unsigned tmask = __ballot_sync(FULL, pass2);
 #ifdef NND_PR_STATS
       n_tile += __popc(tmask);
@@ -362,6 +390,7 @@ __global__ void __launch_bounds__(32 * kPrWarps) nnd_pr_search_kernel(PrSearch p
         if (__any_sync(FULL, !(pr_point_box(mx, my, mz, bx) > best))) {  // every query of the warp is some lane's
           pr_scan_tile(tpts + (long long)t * kPrTile, grp, nqx, nqy, nqz, one, bk);
           mine();
+          share();
           bmax = __uint_as_float(__reduce_max_sync(FULL, __float_as_uint(best)));
 #ifdef NND_PR_STATS
           ++n_scan;
@@ -379,8 +408,17 @@ __global__ void __launch_bounds__(32 * kPrWarps) nnd_pr_search_kernel(PrSearch p
   }
 #endif
   // ---- epilogue: my_lib.cpp:16 (k = 0 is accepted unconditionally) and the scatter to the original query order
+  if (SPLIT > 1) {  // merge the warps' keys; warp 0 writes
+    atomicMin(&key_s[qi], mine());
+    __syncthreads();
+    if (warp != 0) return;
+  }
   if (wq + slot * kPrQPL + grp < nq) {
-    const unsigned long long k = mine();
+    unsigned long long k = mine();
+    if (SPLIT > 1) {
+      k = key_s[qi];
+      best = __uint_as_float((unsigned)(k >> 32));
+    }
     const float* t0p = p.t.xyz + (long long)batch * p.t.n * 3;
     const float dx = __fsub_rn(__ldg(t0p), mx), dy = __fsub_rn(__ldg(t0p + 1), my), dz = __fsub_rn(__ldg(t0p + 2), mz);
     const float d0 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
