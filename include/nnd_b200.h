@@ -160,6 +160,11 @@ size_t nnd_pruned_workspace_bytes(int b, int n, int m);
 int nnd_forward_pruned_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int m,
                                 float *dist1, float *dist2, int32_t *idx1, int32_t *idx2,
                                 void *workspace, size_t workspace_bytes, void *stream);
+/* Tuning / test knob of the pruned search: whether the 4 warps of a CTA share one group of 32 queries (each taking a
+ * quarter of the target tiles) or own a group each.  0 = chosen from the problem size (default: shared below 16 384
+ * groups per call and for target clouds of at least 65 536 points), 1 = never, 2 = always.  Results are bit-identical.
+ * Returns the previous mode; other values only query. */
+int nnd_set_pruned_share(int mode);
 /* One direction of the same search (the pruned twin of nnd_query_cuda_f32): for every query point its nearest target
  * point.  workspace = nnd_pruned_workspace_bytes(b, nq, nt). */
 int nnd_query_pruned_cuda_f32(const float *query, const float *target, int b, int nq, int nt,

@@ -1422,14 +1422,8 @@ inline size_t pr_need(int b, int n, int m) {
 }
 
 // Query groups (b * ceil(n / 32)) below which the warps of a CTA share a group (nnd_pr_search_kernel<kPrWarps>).
-// NND_B200_PR_SPLIT_BELOW overrides (0 = never share; A/B measurements).
-inline long long pr_split_below() {
-  static const long long v = [] {
-    const char* e = getenv("NND_B200_PR_SPLIT_BELOW");
-    return e ? atoll(e) : 16384ll;
-  }();
-  return v;
-}
+constexpr long long kPrShareBelow = 16384;
+std::atomic<int> g_pr_share{0};  // nnd_set_pruned_share: 0 = by size (default), 1 = never, 2 = always
 
 // Sort one cloud along the curve and build its tiles; `keys_in` is scratch.  Returns the first CUDA error.
 int pr_prepare(PrCloud& c, int b, unsigned long long* keys_in, const unsigned* blo, const unsigned* bhi, int kb, int end_bit,
@@ -1512,7 +1506,8 @@ int pruned_forward_impl(const float* xyz1, int n, const float* xyz2, int m, int 
     // repeated box tests would dominate).  Measured, profiles/r02_pruned_split_ab.txt: C3 0.67 -> 0.48 ms, C5
     // 0.87-1.42 -> 0.74-0.88 ms, C4 2.62 / 2.86 -> 2.41 / 2.24 ms; C2 0.95 -> 1.02 ms if it shared.
     const long long groups = ((long long)sp.q.n + 31) / 32;
-    const bool shared_groups = pr_split_below() > 0 && (groups * b < pr_split_below() || sp.t.n >= 65536);
+    const int share_mode = g_pr_share.load(std::memory_order_relaxed);
+    const bool shared_groups = share_mode == 2 || (share_mode == 0 && (groups * b < kPrShareBelow || sp.t.n >= 65536));
     if (!shared_groups) {
       const unsigned gx = (unsigned)((groups + kPrWarps - 1) / kPrWarps);
       nnd_pr_search_kernel<1><<<dim3(gx, (unsigned)b), 32 * kPrWarps, 0, st>>>(sp);
@@ -1677,6 +1672,12 @@ int nnd_forward_warm_cuda_f32(const float* xyz1, const float* xyz2, int b, int n
   int rc = forward_rows_impl(xyz1, n, xyz2, m, b, 0, n, dist1, idx1, colkeys, workspace, rows_bytes, st, hint_idx2);
   if (rc) return rc;
   return finalize_cols_impl(xyz1, n, xyz2, m, b, colkeys, dist2, idx2, st);
+}
+
+int nnd_set_pruned_share(int mode) {
+  const int before = g_pr_share.load();
+  if (mode >= 0 && mode <= 2) g_pr_share.store(mode);
+  return before;
 }
 
 size_t nnd_pruned_workspace_bytes(int b, int n, int m) {

@@ -76,6 +76,35 @@ def test_pruned_query_one_direction(cuda_lib, device):
     assert got[0].cpu().numpy()[:, :3000].tobytes() == w[0].tobytes() and got[1].cpu().numpy()[:, :3000].tobytes() == w[1].tobytes()
 
 
+@pytest.mark.parametrize("share", [1, 2])  # one query group per warp / one per CTA, whatever the size
+def test_pruned_both_group_mappings(share, cuda_lib, device):
+    """Every shape class through BOTH search kernels (nnd_set_pruned_share), incl. ties and non-finite points."""
+    before = cuda_lib.nnd_set_pruned_share(share)
+    try:
+        for kind, b, n, m in (("lattice", 2, 3000, 2500), ("crosscopy", 1, 20000, 17001), ("duplicates", 3, 65, 700),
+                              ("clustered", 1, 33, 40000), ("tiny", 2, 700, 900)):
+            x1, x2 = synthetic.make_pair(kind, b, n, m, 12)
+            got = pruned(x1, x2, device)
+            assert_forward_exact(got, oracle.forward(x1.numpy(), x2.numpy(), threads=8), what=f"share {share} {kind}: ")
+        rng = np.random.default_rng(7 + share)
+        for case in range(6):  # NaN / +-inf / overflowing values sprinkled at random, sometimes at index 0
+            b, n, m = int(rng.integers(1, 3)), int(rng.integers(40, 4000)), int(rng.integers(40, 4000))
+            x1 = rng.random((b, n, 3), dtype=np.float32)
+            x2 = rng.random((b, m, 3), dtype=np.float32)
+            for x in (x1, x2):
+                k = int(rng.integers(1, 12))
+                pos = rng.integers(0, x.shape[1], size=k)
+                pos[0] = 0 if case % 2 else pos[0]
+                x[rng.integers(0, b, size=k), pos, rng.integers(0, 3, size=k)] = rng.choice(
+                    np.array([np.nan, np.inf, -np.inf, 3e19, -3e19], np.float32), size=k)
+            d1, d2, i1, i2 = pruned(x1, x2, device)
+            w1, w2, j1, j2 = oracle.forward(x1, x2)
+            assert np.array_equal(i1, j1) and np.array_equal(i2, j2), (share, case)
+            assert _same_with_nans(d1, w1) and _same_with_nans(d2, w2), (share, case)
+    finally:
+        cuda_lib.nnd_set_pruned_share(before)
+
+
 def test_pruned_empty_clouds(cuda_lib, device):
     x1 = synthetic.uniform(2, 40, 1)
     e = torch.zeros(2, 0, 3)
