@@ -1399,9 +1399,10 @@ int launch_grad(const GradParams& gp, cudaStream_t st) {
 namespace {
 inline int pr_tiles(int n) { return (n + kPrTile - 1) / kPrTile; }
 inline int pr_stiles(int n) { return (pr_tiles(n) + kPrSuper - 1) / kPrSuper; }
+inline int pr_ltiles(int n) { return (pr_stiles(n) + kPrSuper - 1) / kPrSuper; }
 struct PrSizes {
-  size_t keys, pts, tbox, sbox, tcode;
-  size_t total() const { return 2 * keys + pts + tbox + sbox + tcode; }
+  size_t keys, pts, tbox, sbox, lbox, tcode;
+  size_t total() const { return 2 * keys + pts + tbox + sbox + lbox + tcode; }
 };
 inline PrSizes pr_sizes(int b, int n) {
   PrSizes z;
@@ -1409,6 +1410,7 @@ inline PrSizes pr_sizes(int b, int n) {
   z.pts = align_up((size_t)b * pr_tiles(n) * kPrTile * sizeof(float4), 256);
   z.tbox = align_up((size_t)b * pr_tiles(n) * sizeof(PrBox), 256);
   z.sbox = align_up((size_t)b * pr_stiles(n) * sizeof(PrBox), 256);
+  z.lbox = align_up((size_t)b * pr_ltiles(n) * sizeof(PrBox), 256);
   z.tcode = align_up((size_t)b * pr_tiles(n) * sizeof(unsigned), 256);
   return z;
 }
@@ -1436,8 +1438,9 @@ int pr_prepare(PrCloud& c, int b, unsigned long long* keys_in, const unsigned* b
                                                  32, end_bit, st);
   if (e != cudaSuccess) return (int)e;
   nnd_pr_gather_kernel<<<dim3((unsigned)c.tiles, (unsigned)b), kPrTile, 0, st>>>(c);
-  nnd_pr_super_kernel<<<dim3((unsigned)((c.stiles + 3) / 4), (unsigned)b), 128, 0, st>>>(c);
-  g_launches += 3;  // + the library's sort passes
+  nnd_pr_super_kernel<<<dim3((unsigned)((c.stiles + 3) / 4), (unsigned)b), 128, 0, st>>>(c.tbox, c.tiles, c.sbox, c.stiles);
+  nnd_pr_super_kernel<<<dim3((unsigned)((c.ltiles + 3) / 4), (unsigned)b), 128, 0, st>>>(c.sbox, c.stiles, c.lbox, c.ltiles);
+  g_launches += 4;  // + the library's sort passes
   return check_last(cudaGetLastError());
 }
 
@@ -1464,6 +1467,7 @@ int pruned_forward_impl(const float* xyz1, int n, const float* xyz2, int m, int 
     c[i].n = cnt[i];
     c[i].tiles = pr_tiles(cnt[i]);
     c[i].stiles = pr_stiles(cnt[i]);
+    c[i].ltiles = pr_ltiles(cnt[i]);
     c[i].keys = (unsigned long long*)w;
     w += z.keys;
     c[i].pts = (float4*)w;
@@ -1472,6 +1476,8 @@ int pruned_forward_impl(const float* xyz1, int n, const float* xyz2, int m, int 
     w += z.tbox;
     c[i].sbox = (PrBox*)w;
     w += z.sbox;
+    c[i].lbox = (PrBox*)w;
+    w += z.lbox;
     c[i].tcode = (unsigned*)w;
     w += z.tcode;
   }

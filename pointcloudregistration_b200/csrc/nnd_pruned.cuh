@@ -45,13 +45,14 @@ struct __align__(32) PrBox {  // lo.xyz, hi.xyz (+ padding to 32 bytes: two 16-b
 struct PrCloud {
   const float* xyz;          // [b][n][3] original order
   int n;                     // points per batch element
-  int tiles, stiles;         // tiles / super-tiles per batch element
+  int tiles, stiles, ltiles; // tiles / super-tiles (32 tiles) / large tiles (32 super-tiles) per batch element
   unsigned long long* keys;  // [b * n] sorted keys: (batch : morton) << 32 | original index
   float4* pts;               // [b][tiles * kPrTile]  sorted points in PAIR layout: points 2p, 2p+1 are the two float4
                              //   {x0, x1, y0, y1} {z0, z1, w0, w1}, w = original index (int bits) -- operands of the
                              //   packed f32x2 sequence; padded with copies of the last point carrying index INT_MAX
   PrBox* tbox;               // [b][tiles]
   PrBox* sbox;               // [b][stiles]
+  PrBox* lbox;               // [b][ltiles]   (65 536 points each: keeps the walk O(N/65536 + log) per warp at 10^7..10^8 points)
   unsigned* tcode;           // [b][tiles]  high key word of the first point of the tile
 };
 
@@ -177,23 +178,24 @@ __global__ void __launch_bounds__(kPrTile) nnd_pr_gather_kernel(PrCloud c) {
   }
 }
 
-// One warp per super-tile: union of its (up to) 32 tile boxes.
-__global__ void __launch_bounds__(128) nnd_pr_super_kernel(PrCloud c) {
+// One warp per output box: union of (up to) 32 consecutive input boxes (tiles -> super-tiles -> large tiles).
+__global__ void __launch_bounds__(128) nnd_pr_super_kernel(const PrBox* __restrict__ in, int nin, PrBox* __restrict__ out,
+                                                           int nout) {
   const int batch = blockIdx.y;
-  const int st = blockIdx.x * 4 + (threadIdx.x >> 5);
-  if (st >= c.stiles) return;
+  const int o = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (o >= nout) return;
   const int lane = threadIdx.x & 31;
-  const int tile = st * kPrSuper + lane;
+  const int i = o * kPrSuper + lane;
   const float INF = __int_as_float(0x7f800000);
   PrBox bx{INF, INF, INF, -INF, -INF, -INF, 0.f, 0.f};
-  if (tile < c.tiles) bx = c.tbox[(long long)batch * c.tiles + tile];
+  if (i < nin) bx = in[(long long)batch * nin + i];
   bx.lx = pr_wmin(bx.lx);
   bx.ly = pr_wmin(bx.ly);
   bx.lz = pr_wmin(bx.lz);
   bx.hx = pr_wmax(bx.hx);
   bx.hy = pr_wmax(bx.hy);
   bx.hz = pr_wmax(bx.hz);
-  if (lane == 0) c.sbox[(long long)batch * c.stiles + st] = bx;
+  if (lane == 0) out[(long long)batch * nout + o] = bx;
 }
 
 // Lower bound of the fl-evaluated squared distance between any point of box a and any point of box b, made safe
@@ -326,7 +328,8 @@ __global__ void __launch_bounds__(32 * kPrWarps) nnd_pr_search_kernel(PrSearch p
   qb.hy = pr_wmax(qb.hy);
   qb.hz = pr_wmax(qb.hz);
 
-  const int T = p.t.tiles, ST = p.t.stiles;
+  const int T = p.t.tiles, ST = p.t.stiles, LT = p.t.ltiles;
+  const PrBox* lbox = p.t.lbox + (long long)batch * LT;
   const float4* tpts = p.t.pts + (long long)batch * T * kPrTile;
   const PrBox* tbox = p.t.tbox + (long long)batch * T;
   const PrBox* sbox = p.t.sbox + (long long)batch * ST;
@@ -360,8 +363,14 @@ __global__ void __launch_bounds__(32 * kPrWarps) nnd_pr_search_kernel(PrSearch p
 #endif
   float bmax = __uint_as_float(__reduce_max_sync(FULL, __float_as_uint(best)));  // best >= +0 or +inf: bit order = value order
 
-  // ---- super-tiles -> tiles -> per-query test -> scan
-  for (int sb = 0; sb < ST; sb += 32) {
+  // ---- large tiles -> super-tiles -> tiles -> per-query test -> scan
+  for (int lb = 0; lb < LT; lb += 32) {
+   bool lpass = false;
+   if (lb + lane < LT) lpass = !(pr_box_box(qb, lbox[lb + lane]) > bmax);
+   unsigned lmask = __ballot_sync(FULL, lpass);
+   while (lmask) {
+    const int sb = (lb + __ffs(lmask) - 1) * kPrSuper;  // first super-tile of this large tile
+    lmask &= lmask - 1;
     const int st = sb + lane;
     bool pass = false;
     if (st < ST) pass = !(pr_box_box(qb, sbox[st]) > bmax);
@@ -398,6 +407,7 @@ __global__ void __launch_bounds__(32 * kPrWarps) nnd_pr_search_kernel(PrSearch p
         }
       }
     }
+   }
   }
 #ifdef NND_PR_STATS
   if (lane == 0) {

@@ -68,7 +68,7 @@ def test_pruned_query_one_direction(cuda_lib, device):
     before = F.set_search_mode("pruned")
     try:
         got = F.nnd_query_raw(qd, td)
-        assert cuda_lib.nnd_last_launch_count() == 9 != brute_launches  # 2 boxes + 2 x (code, gather, super) + 1 search
+        assert cuda_lib.nnd_last_launch_count() == 11 != brute_launches  # 2 boxes + 2 x (code, gather, 2 box levels) + 1 search
     finally:
         F.set_search_mode(before)
     assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
@@ -164,7 +164,7 @@ def test_search_mode_switch_routes_the_public_api(cuda_lib, device):
     try:
         assert F.search_mode() == "pruned"
         got = NND.nnd_with_idx(a, c)
-        assert cuda_lib.nnd_last_launch_count() in range(8, 12)  # 2 boxes + 2 x (code, gather, super) + 2 searches
+        assert cuda_lib.nnd_last_launch_count() == 12  # 2 boxes + 2 x (code, gather, 2 box levels) + 2 searches
         (got[0].mean() + got[1].mean()).backward()
         small = NND.nnd_with_idx(a[:, :500], c[:, :400])  # below the thresholds: the single-launch kernels
         assert cuda_lib.nnd_last_launch_count() == 1
@@ -200,3 +200,29 @@ def test_pruned_c2_batch_digest(cuda_lib, device):
     got = pruned(x1, x2, device)
     for k, v in zip(("dist1", "dist2", "idx1", "idx2"), got):
         assert sha(v) == meta["sha256"][k], f"c2: pruned {k} differs from the reference's full-size output"
+
+
+def test_pruned_ten_million_points_sampled_rows(cuda_lib, device):
+    """N = M = 10^7 (the brute-force scan would take ~25 s per forward): three box levels.  160 sampled rows per direction
+    against the oracle, plus the size-independent properties: the reported neighbour is at the reported distance, and a
+    second call on the swapped clouds returns the swapped results."""
+    n = 10_000_000
+    g = torch.Generator().manual_seed(4242)
+    x1 = torch.rand(1, n, 3, generator=g)
+    x2 = torch.rand(1, n, 3, generator=g)
+    x2[0, 5_000_000:5_000_100] = x1[0, 100:200]  # exact copies: distance 0 at a known index
+    a, c = x1.to(device), x2.to(device)
+    d1, d2, i1, i2 = F.nnd_forward_pruned_raw(a, c)
+    e2, e1, j2, j1 = F.nnd_forward_pruned_raw(c, a)
+    torch.cuda.synchronize()
+    assert torch.equal(d1, e1) and torch.equal(i1, j1) and torch.equal(d2, e2) and torch.equal(i2, j2)
+    assert float(d2[0, 5_000_000:5_000_100].abs().max()) == 0.0 and torch.equal(i2[0, 5_000_000:5_000_100].cpu(),
+                                                                                torch.arange(100, 200, dtype=torch.int32))
+    rows = torch.randperm(n, generator=g)[:160].sort().values
+    w1 = oracle.query(x1[:, rows].numpy(), x2.numpy(), threads=16)
+    w2 = oracle.query(x2[:, rows].numpy(), x1.numpy(), threads=16)
+    assert d1[:, rows].cpu().numpy().tobytes() == w1[0].tobytes() and i1[:, rows].cpu().numpy().tobytes() == w1[1].tobytes()
+    assert d2[:, rows].cpu().numpy().tobytes() == w2[0].tobytes() and i2[:, rows].cpu().numpy().tobytes() == w2[1].tobytes()
+    nb = c[0, i1[0].long()]  # the reported neighbour is at the reported distance (same rounding sequence in torch fp32)
+    dx = nb - a[0]
+    assert torch.equal((dx[:, 0] * dx[:, 0] + dx[:, 1] * dx[:, 1]) + dx[:, 2] * dx[:, 2], d1[0])

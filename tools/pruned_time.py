@@ -46,3 +46,11 @@ for name, kind, b, n, cfg in shapes:
     tp = best_of(lambda: F.nnd_forward_pruned_raw(a, c), 5)
     print(f"{name:20s} B={b:3d} N=M={n:8d}: brute {tb:9.3f} ms | pruned {tp:9.3f} ms | x{tb / tp:7.1f} | "
           f"{'bit-identical' if same else 'DIFFERENT'}", flush=True)
+
+if not only or "10M" in only:  # beyond the brute-force scan's reach (~25 s per forward): pruned only
+    for kind in ("uniform", "clustered"):
+        n = 10_000_000
+        x1, x2 = synthetic.make_pair(kind, 1, n, n, 4)
+        a, c = x1.to(dev), x2.to(dev)
+        tp = best_of(lambda: F.nnd_forward_pruned_raw(a, c), 3)
+        print(f"10M {kind:12s}     B=  1 N=M={n:8d}: brute (extrapolated) {243.0 * 100:9.0f} ms | pruned {tp:9.3f} ms", flush=True)
