@@ -160,6 +160,17 @@ size_t nnd_pruned_workspace_bytes(int b, int n, int m);
 int nnd_forward_pruned_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int m,
                                 float *dist1, float *dist2, int32_t *idx1, int32_t *idx2,
                                 void *workspace, size_t workspace_bytes, void *stream);
+/* The pruned search inside a registration loop (registration.py:231-261: one cloud moves a little per iteration, the other
+ * never): nnd_forward_pruned_cuda_f32 with parts of the PREVIOUS call's preparation reused.  `reuse` bits:
+ *   1 = keep xyz1's curve ORDER from the previous call (skip its sort).  Its points and every box are rebuilt from the
+ *       CURRENT coordinates, so the results stay exact however far the cloud has moved -- a stale order only costs pruning
+ *       power; re-sort (clear the bit) every few dozen iterations;
+ *   2 = xyz2 is bit-for-bit unchanged since the previous call: all of its preparation is reused as it is.
+ * The workspace must be the one the previous call used, untouched in between, with the same b, n, m (n, m > 0).
+ * reuse = 0 is nnd_forward_pruned_cuda_f32.  RESULTS ARE THE SAME BITS for every value of `reuse` that is used as described. */
+int nnd_forward_pruned_reuse_cuda_f32(const float *xyz1, const float *xyz2, int b, int n, int m,
+                                      float *dist1, float *dist2, int32_t *idx1, int32_t *idx2,
+                                      void *workspace, size_t workspace_bytes, int reuse, void *stream);
 /* Tuning / test knob of the pruned search: whether the 4 warps of a CTA share one group of 32 queries (each taking a
  * quarter of the target tiles) or own a group each.  0 = chosen from the problem size (default: shared below 16 384
  * groups per call and for target clouds of at least 65 536 points), 1 = never, 2 = always.  Results are bit-identical.

@@ -30,6 +30,8 @@ SIGNATURES = {
                                            c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "nnd_pruned_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "nnd_set_pruned_share": (c_int, [c_int]),
+    "nnd_forward_pruned_reuse_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                                   c_void_p, c_void_p, c_size_t, c_int, c_void_p]),
     "nnd_forward_pruned_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                              c_void_p, c_void_p, c_size_t, c_void_p]),
     "nnd_query_pruned_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,

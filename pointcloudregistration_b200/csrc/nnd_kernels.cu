@@ -1428,25 +1428,33 @@ constexpr long long kPrShareBelow = 16384;
 std::atomic<int> g_pr_share{0};  // nnd_set_pruned_share: 0 = by size (default), 1 = never, 2 = always
 
 // Sort one cloud along the curve and build its tiles; `keys_in` is scratch.  Returns the first CUDA error.
+// keep_order: the sorted keys of a previous call stay as they are (nnd_forward_pruned_reuse_cuda_f32); the points and
+// every box are rebuilt from the cloud's CURRENT coordinates, so a stale order costs pruning power, never exactness.
 int pr_prepare(PrCloud& c, int b, unsigned long long* keys_in, const unsigned* blo, const unsigned* bhi, int kb, int end_bit,
-               void* temp, size_t temp_bytes, int sms, cudaStream_t st) {
+               void* temp, size_t temp_bytes, int sms, cudaStream_t st, bool keep_order) {
   const long long count = (long long)b * c.n;
   long long bl = ((long long)c.n + 255) / 256;
   const unsigned blocks = (unsigned)(bl > 8ll * sms ? 8ll * sms : bl < 1 ? 1 : bl);
-  nnd_pr_code_kernel<<<dim3(blocks, (unsigned)b), 256, 0, st>>>(c.xyz, c.n, blo, bhi, kb, keys_in);
-  cudaError_t e = cub::DeviceRadixSort::SortKeys(temp, temp_bytes, (const unsigned long long*)keys_in, c.keys, (int)count,
-                                                 32, end_bit, st);
-  if (e != cudaSuccess) return (int)e;
+  if (!keep_order) {
+    nnd_pr_code_kernel<<<dim3(blocks, (unsigned)b), 256, 0, st>>>(c.xyz, c.n, blo, bhi, kb, keys_in);
+    ++g_launches;
+    cudaError_t e = cub::DeviceRadixSort::SortKeys(temp, temp_bytes, (const unsigned long long*)keys_in, c.keys, (int)count,
+                                                   32, end_bit, st);
+    if (e != cudaSuccess) return (int)e;
+  }
   nnd_pr_gather_kernel<<<dim3((unsigned)c.tiles, (unsigned)b), kPrTile, 0, st>>>(c);
   nnd_pr_super_kernel<<<dim3((unsigned)((c.stiles + 3) / 4), (unsigned)b), 128, 0, st>>>(c.tbox, c.tiles, c.sbox, c.stiles);
   nnd_pr_super_kernel<<<dim3((unsigned)((c.ltiles + 3) / 4), (unsigned)b), 128, 0, st>>>(c.sbox, c.stiles, c.lbox, c.ltiles);
-  g_launches += 4;  // + the library's sort passes
+  g_launches += 3;  // + the library's sort passes
   return check_last(cudaGetLastError());
 }
 
 // ndir == 2: both directions; ndir == 1: only cloud 1's points against cloud 2 (nnd_query_pruned_cuda_f32).
+// reuse (nnd_forward_pruned_reuse_cuda_f32): bit 0 = keep cloud 1's curve order, bit 1 = cloud 2 unchanged (all of its
+// preparation in the workspace is still valid).
 int pruned_forward_impl(const float* xyz1, int n, const float* xyz2, int m, int b, int ndir, float* dist1, int32_t* idx1,
-                        float* dist2, int32_t* idx2, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+                        float* dist2, int32_t* idx2, void* workspace, size_t workspace_bytes, cudaStream_t st,
+                        int reuse = 0) {
   DeviceInfo di;
   int rc = device_info(&di);
   if (rc) return rc;
@@ -1491,17 +1499,23 @@ int pruned_forward_impl(const float* xyz1, int n, const float* xyz2, int m, int 
   void* temp = w;
   const size_t temp_bytes = pr_temp_bytes(b, n, m);
 
-  cudaError_t e = cudaMemsetAsync(blo, 0xff, (size_t)b * 3 * sizeof(unsigned), st);
-  if (e == cudaSuccess) e = cudaMemsetAsync(bhi, 0, (size_t)b * 3 * sizeof(unsigned), st);
-  if (e != cudaSuccess) return (int)e;
-  for (int i = 0; i < 2; ++i) {
-    long long bl = ((long long)cnt[i] + 255) / 256;
-    const unsigned blocks = (unsigned)(bl > 8ll * di.sms ? 8ll * di.sms : bl < 1 ? 1 : bl);
-    nnd_pr_bbox_kernel<<<dim3(blocks, (unsigned)b), 256, 0, st>>>(src[i], cnt[i], blo, bhi);
-    ++g_launches;
+  const bool keep1 = (reuse & 1) != 0, same2 = (reuse & 2) != 0;
+  if (!same2) {  // a new joint box; with cloud 2 reused the old one stays (its codes were cut with it; points of cloud 1
+                 // that left it clamp to the border cells)
+    cudaError_t e = cudaMemsetAsync(blo, 0xff, (size_t)b * 3 * sizeof(unsigned), st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(bhi, 0, (size_t)b * 3 * sizeof(unsigned), st);
+    if (e != cudaSuccess) return (int)e;
+    for (int i = 0; i < 2; ++i) {
+      long long bl = ((long long)cnt[i] + 255) / 256;
+      const unsigned blocks = (unsigned)(bl > 8ll * di.sms ? 8ll * di.sms : bl < 1 ? 1 : bl);
+      nnd_pr_bbox_kernel<<<dim3(blocks, (unsigned)b), 256, 0, st>>>(src[i], cnt[i], blo, bhi);
+      ++g_launches;
+    }
   }
-  for (int i = 0; i < 2; ++i) {
-    rc = pr_prepare(c[i], b, keys_in, blo, bhi, kb, end_bit, temp, temp_bytes, di.sms, st);
+  rc = pr_prepare(c[0], b, keys_in, blo, bhi, kb, end_bit, temp, temp_bytes, di.sms, st, keep1);
+  if (rc) return rc;
+  if (!same2) {
+    rc = pr_prepare(c[1], b, keys_in, blo, bhi, kb, end_bit, temp, temp_bytes, di.sms, st, false);
     if (rc) return rc;
   }
   for (int dir = 0; dir < ndir; ++dir) {
@@ -1703,6 +1717,18 @@ int nnd_forward_pruned_cuda_f32(const float* xyz1, const float* xyz2, int b, int
   if (m == 0) return zero_outputs(dist1, idx1, (long long)b * n, st);
   if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2 || !workspace) return NND_EINVAL;
   return pruned_forward_impl(xyz1, n, xyz2, m, b, 2, dist1, idx1, dist2, idx2, workspace, workspace_bytes, st);
+}
+
+int nnd_forward_pruned_reuse_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int m, float* dist1, float* dist2,
+                                      int32_t* idx1, int32_t* idx2, void* workspace, size_t workspace_bytes, int reuse,
+                                      void* stream) {
+  g_launches = 0;
+  if (reuse < 0 || reuse > 3) return NND_EINVAL;
+  if (!sizes_ok(b, n, m) || b <= 0 || n <= 0 || m <= 0) return NND_EINVAL;  // a loop over fixed, non-empty clouds
+  if ((long long)b * n > 0x7fffffffLL - 1024 || (long long)b * m > 0x7fffffffLL - 1024) return NND_EINVAL;
+  if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2 || !workspace) return NND_EINVAL;
+  return pruned_forward_impl(xyz1, n, xyz2, m, b, 2, dist1, idx1, dist2, idx2, workspace, workspace_bytes,
+                             (cudaStream_t)stream, reuse);
 }
 
 int nnd_query_pruned_cuda_f32(const float* query, const float* target, int b, int nq, int nt, float* dist, int32_t* idx,

@@ -26,9 +26,12 @@ from .functional import _pruned_route, _stream_ptr, chamfer_reduce_workspace
 
 class ChamferLoop:
     def __init__(self, b: int, n: int, m: int, device, trunc: float = 1e9, use_graph: bool = True, warm: bool = True,
-                 search: str = None):
+                 search: str = None, resort_every: int = 32):
         """search: 'brute' (the reference's scan), 'pruned' (the exact pruned search, same bits -- DESIGN.md 4.7), or
-        None = functional.search_mode() with its size thresholds."""
+        None = functional.search_mode() with its size thresholds.
+        resort_every (pruned search): the target cloud is prepared once per set_target(); the moving cloud keeps its curve
+        order between steps and is re-sorted every resort_every-th step (nnd_forward_pruned_reuse_cuda_f32: the results
+        never depend on it, a stale order only prunes less).  0 = sort both clouds in every step."""
         self.b, self.n, self.m, self.trunc = b, n, m, float(trunc)
         self.warm = bool(warm)  # hand the previous iteration's idx2 to the forward as a hint (results never depend on it)
         self.device = dev = torch.device(device)
@@ -52,18 +55,22 @@ class ChamferLoop:
             raise ValueError("the pruned search needs b <= 65535 and b*n, b*m < 2^31")
         self._ws = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=dev)
         self._rws = chamfer_reduce_workspace(dev)
-        self.graph = None
+        self.graph = None   # brute-force body / the pruned body with reuse = 0
+        self._graphs = {}   # pruned search: one captured body per `reuse` value (0, 2, 3)
         self.use_graph = use_graph
         self.replays = 0
+        self.resort_every = max(int(resort_every), 0)
+        self._target_ready = False  # the workspace holds the current target's tiles
+        self._since_sort = 0
 
     # what one iteration computes (also the eager path when use_graph is False): 3-4 forward launches, the fused
     # mask + mean/mean reduction + d loss/d dist, 2 memsets + the gradient kernel -- all over static buffers
-    def _body(self):
+    def _body(self, reuse: int = 0):
         lib, st = self.lib, _stream_ptr(self.device)
         b, n, m = self.b, self.n, self.m
         # warm start: the loop's own idx2 of the previous iteration is the hint (any content is safe, results do not
         # depend on it; the first iteration sees zeros = "try row 0")
-        self._forward(st)
+        self._forward(st, reuse)
         # point_reduction = mean (divide by the cloud length), batch_reduction = mean, both directions summed
         s1, s2 = 1.0 / (max(n, 1) * max(b, 1)), 1.0 / (max(m, 1) * max(b, 1))
         rc = lib.nnd_chamfer_reduce_cuda_f32(self.dist1.data_ptr(), self.dist2.data_ptr(), b, n, m, self.trunc, s1, s2,
@@ -75,14 +82,14 @@ class ChamferLoop:
                                        self.grad_y.data_ptr(), st)
         _cabi.check(rc, "nnd_backward_cuda_f32")
 
-    def _forward(self, st) -> None:
+    def _forward(self, st, reuse: int = 0) -> None:
         """nnd forward over the static buffers on raw stream `st` (capturable: no allocation, no host read)."""
         lib, b, n, m = self.lib, self.b, self.n, self.m
         if self.pruned:
-            rc = lib.nnd_forward_pruned_cuda_f32(self.x.data_ptr(), self.y.data_ptr(), b, n, m, self.dist1.data_ptr(),
-                                                 self.dist2.data_ptr(), self.idx1.data_ptr(), self.idx2.data_ptr(),
-                                                 self._ws.data_ptr(), self._ws.numel(), st)
-            _cabi.check(rc, "nnd_forward_pruned_cuda_f32")
+            rc = lib.nnd_forward_pruned_reuse_cuda_f32(self.x.data_ptr(), self.y.data_ptr(), b, n, m, self.dist1.data_ptr(),
+                                                       self.dist2.data_ptr(), self.idx1.data_ptr(), self.idx2.data_ptr(),
+                                                       self._ws.data_ptr(), self._ws.numel(), int(reuse), st)
+            _cabi.check(rc, "nnd_forward_pruned_reuse_cuda_f32")
             return
         rc = lib.nnd_forward_warm_cuda_f32(self.x.data_ptr(), self.y.data_ptr(), b, n, m, self.dist1.data_ptr(),
                                            self.dist2.data_ptr(), self.idx1.data_ptr(), self.idx2.data_ptr(),
@@ -90,30 +97,47 @@ class ChamferLoop:
                                            self._ws.numel(), st)
         _cabi.check(rc, "nnd_forward_warm_cuda_f32")
 
-    def _capture(self):
+    def _capture(self, reuse: int = 0):
         s = torch.cuda.Stream(self.device)
         s.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(s):  # warm-up outside capture (lazy module loads, func attributes)
             for _ in range(2):
-                self._body()
+                self._body(reuse)
         torch.cuda.current_stream(self.device).wait_stream(s)
-        self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
-            self._body()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._body(reuse)
+        self._graphs[reuse] = g
+        if reuse == 0:
+            self.graph = g
+
+    def _next_reuse(self) -> int:
+        """Which parts of the previous step's preparation this step may reuse (pruned search only)."""
+        if not self.pruned or self.resort_every == 0 or not self._target_ready:
+            r = 0                      # everything from scratch: the first step after set_target()
+        elif self._since_sort + 1 >= self.resort_every:
+            r = 2                      # target tiles kept, the moving cloud re-sorted
+        else:
+            r = 3                      # ... and its order kept too
+        self._since_sort = 0 if r != 3 else self._since_sort + 1
+        self._target_ready = True
+        return r
 
     def set_target(self, y: torch.Tensor) -> None:
         self.y.copy_(y.detach().reshape(self.b, self.m, 3), non_blocking=True)
+        self._target_ready = False
 
     def step(self, x: torch.Tensor):
         """loss (0-dim device tensor, valid until the next step) and d loss / d x [b,n,3]; no host sync."""
         self.x.copy_(x.detach().reshape(self.b, self.n, 3), non_blocking=True)  # stream-ordered, also from pinned host memory
+        reuse = self._next_reuse()
         with torch.cuda.device(self.device):
             if not self.use_graph:
-                self._body()
+                self._body(reuse)
             else:
-                if self.graph is None:
-                    self._capture()
-                self.graph.replay()
+                if reuse not in self._graphs:
+                    self._capture(reuse)
+                self._graphs[reuse].replay()
         self.replays += 1
         return self.loss, self.grad_x
 

@@ -169,3 +169,36 @@ def test_loop_with_the_pruned_search_is_bit_identical_to_the_brute_force_loop(cu
         assert (ga - gb).abs().max() <= 1e-5 * scale  # atomic summation order
         xa = xa - 5.0 * gb
     assert a.replays == 8
+
+
+@pytest.mark.parametrize("use_graph", [True, False])
+def test_pruned_loop_reuses_the_target_tiles_and_a_stale_source_order(cuda_lib, device, use_graph):
+    """nnd_forward_pruned_reuse_cuda_f32 through ChamferLoop(search='pruned', resort_every=4): the target is prepared
+    once per set_target(), the moving cloud keeps its curve order for 3 of 4 steps.  Even with the cloud moving far
+    (every step, plus a jump) every iteration returns the brute-force loop's bits; a new target resets the reuse."""
+    n, m = 20000, 23000
+    x0, y = synthetic.make_pair("clustered", 1, n, m, 98)
+    _, y2 = synthetic.make_pair("uniform", 1, n, m, 99)
+    y, y2 = y.to(device), y2.to(device)
+    a = ndp_loop.ChamferLoop(1, n, m, device, use_graph=use_graph, search="pruned", resort_every=4)
+    b = ndp_loop.ChamferLoop(1, n, m, device, use_graph=use_graph, search="brute")
+    a.set_target(y)
+    b.set_target(y)
+    xa = x0.to(device).clone()
+    seen = []
+    for it in range(14):
+        if it == 9:  # a new target in the middle of the loop
+            a.set_target(y2)
+            b.set_target(y2)
+        la, ga = a.step(xa)
+        lb, gb = b.step(xa)
+        seen.append(a._since_sort)
+        assert torch.equal(a.idx1, b.idx1) and torch.equal(a.idx2, b.idx2), it
+        assert torch.equal(a.dist1, b.dist1) and torch.equal(a.dist2, b.dist2), it
+        assert torch.equal(la, lb), (it, float(la), float(lb))
+        xa = xa - 20.0 * gb
+        if it == 5:  # a jump the stale order knows nothing about (the order is only a pruning aid)
+            xa = xa.flip(1) * 0.5 + 0.3
+    assert seen == [0, 1, 2, 3, 0, 1, 2, 3, 0, 0, 1, 2, 3, 0]  # steps since the moving cloud was last sorted
+    if use_graph:
+        assert sorted(a._graphs) == [0, 2, 3]
