@@ -5,13 +5,14 @@
 // metric of this project is defined on it.  This path returns THE SAME BITS (dist bit-exact, lowest index on ties, the
 // same NaN / inf rules) while evaluating only the pairs that can matter:
 //
-//   * both clouds are sorted along a Morton curve (30-bit codes over the joint bounding box; cub radix sort of
-//     (batch : code : index) keys) and cut into TILES of kPrTile consecutive points with their bounding boxes, and
-//     SUPER-TILES of 32 tiles;
-//   * one WARP owns 32 consecutive sorted queries (a compact box).  It first scans the target tile at its own position
-//     on the curve (good upper bounds), then walks super-tiles -> tiles, skipping every box whose distance lower bound
-//     exceeds the largest current best distance of its lanes, and scans a surviving tile only if some lane's own
-//     point-to-box bound does not exceed that lane's best;
+//   * both clouds are sorted along a Morton curve (<= 30-bit codes over the joint bounding box; cub radix sort of
+//     (batch : code : index) keys) and cut into TILES of kPrTile consecutive points with their bounding boxes,
+//     SUPER-TILES of 32 tiles and LARGE TILES of 32 super-tiles;
+//   * a GROUP of 32 consecutive sorted queries (a compact box) belongs to one warp -- or, for small problems and large
+//     target clouds, to the 4 warps of a CTA, each taking a quarter of the target tiles.  A warp first scans the target
+//     tile at the group's own position on the curve (good upper bounds), then walks large tiles -> super-tiles ->
+//     tiles, skipping every box whose distance lower bound exceeds the largest current best distance of the group's
+//     queries, and scans a surviving tile only if some query's own point-to-box bound does not exceed that query's best;
 //   * a skipped box satisfies  fl-distance(q, t) >= bound > best(q)  for every target t in it and every query q of the
 //     warp, so it holds neither the minimum nor a tie; the bound is the exact box distance evaluated in fp32 and then
 //     shrunk by 2^-20 relative and 2^-100 absolute, which covers the rounding of both sides;
