@@ -15,7 +15,8 @@ PKG_DIR = Path(__file__).resolve().parent
 REPO_ROOT = PKG_DIR.parent
 SOURCES = [PKG_DIR / "csrc" / "nnd_kernels.cu"]
 HEADERS = [REPO_ROOT / "include" / "nnd_b200.h", PKG_DIR / "csrc" / "nnd_sym.cuh", PKG_DIR / "csrc" / "nnd_symc.cuh", PKG_DIR / "csrc" / "nnd_grad.cuh",
-           PKG_DIR / "csrc" / "nnd_grad_exact.cuh", PKG_DIR / "csrc" / "nnd_small.cuh", PKG_DIR / "csrc" / "nnd_hint.cuh"]
+           PKG_DIR / "csrc" / "nnd_grad_exact.cuh", PKG_DIR / "csrc" / "nnd_small.cuh", PKG_DIR / "csrc" / "nnd_hint.cuh",
+           PKG_DIR / "csrc" / "nnd_pruned.cuh"]
 LIB_PATH = PKG_DIR / "libnnd_b200.so"
 
 NVCC_FLAGS = [

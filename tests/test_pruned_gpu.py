@@ -105,6 +105,23 @@ def test_pruned_both_group_mappings(share, cuda_lib, device):
         cuda_lib.nnd_set_pruned_share(before)
 
 
+def test_pruned_workspace_errors(cuda_lib, device):
+    x1, x2 = synthetic.make_pair("uniform", 1, 5000, 4000, 3)
+    a, c = x1.to(device), x2.to(device)
+    outs = [torch.empty(1, 5000, device=device), torch.empty(1, 4000, device=device),
+            torch.empty(1, 5000, dtype=torch.int32, device=device), torch.empty(1, 4000, dtype=torch.int32, device=device)]
+    need = cuda_lib.nnd_pruned_workspace_bytes(1, 5000, 4000)
+    ws = torch.empty(need + 256, dtype=torch.uint8, device=device)
+    args = (a.data_ptr(), c.data_ptr(), 1, 5000, 4000, outs[0].data_ptr(), outs[1].data_ptr(), outs[2].data_ptr(), outs[3].data_ptr())
+    assert cuda_lib.nnd_forward_pruned_cuda_f32(*args, ws.data_ptr(), need - 1, None) == 10002       # too small
+    assert cuda_lib.nnd_forward_pruned_cuda_f32(*args, ws.data_ptr() + 16, need, None) == 10002      # misaligned
+    assert cuda_lib.nnd_forward_pruned_reuse_cuda_f32(*args, ws.data_ptr(), need, 4, None) == 10001  # unknown reuse bits
+    assert cuda_lib.nnd_forward_pruned_cuda_f32(*args, ws.data_ptr(), need, None) == 0
+    torch.cuda.synchronize()
+    want = oracle.forward(x1.numpy(), x2.numpy())
+    assert_forward_exact(tuple(t.cpu().numpy() for t in outs), want)
+
+
 def test_pruned_empty_clouds(cuda_lib, device):
     x1 = synthetic.uniform(2, 40, 1)
     e = torch.zeros(2, 0, 3)
