@@ -76,6 +76,23 @@ int nnd_finalize_cols_cuda_f32(const float *xyz1, const float *xyz2, int b, int 
                                const unsigned long long *colkeys,
                                float *dist2, int32_t *idx2, void *stream);
 
+/* ---- the multi-GPU exchange over PEER MEMORY (new design; the reference has no multi-device path).  One process per GPU;
+ * every rank holds its column keys, dist1 / idx1 (own rows final) and output buffers in memory the other ranks can address
+ * (NVLink / NVSwitch P2P: e.g. torch.distributed._symmetric_memory), and passes HOST arrays of the `world` device pointers,
+ * its own included, in rank order.  nnd_exchange_cols_p2p_cuda_f32 is ONE kernel for "all_reduce(MIN) of the column keys +
+ * nnd_finalize_cols_cuda_f32 + all_gather of dist1 / idx1": rank r merges and finalizes its slice of the columns reading
+ * every rank's keys directly, stores dist2 / idx2 of that slice into every rank's buffers and pushes its own rows
+ * [row_lo, row_hi) of dist1 / idx1 to every rank.  nnd_sum_p2p_cuda_f32 sums `count` floats of every rank's buffer in
+ * place (two-shot, rank order: the same bits on every rank and run to run).  THE CALLER brackets each launch with a
+ * barrier over all ranks on `stream` (before: every rank's inputs are complete; after: every store has landed).
+ * At most nnd_peer_max_ranks() ranks.  Results are bit-identical to the NCCL formulation for any world size. */
+int nnd_peer_max_ranks(void);
+int nnd_exchange_cols_p2p_cuda_f32(const void *const *peer_colkeys, void *const *peer_dist1, void *const *peer_idx1,
+                                   void *const *peer_dist2, void *const *peer_idx2, int world, int rank,
+                                   const float *xyz1, const float *xyz2, int b, int n, int m,
+                                   int row_lo, int row_hi, void *stream);
+int nnd_sum_p2p_cuda_f32(void *const *peer_bufs, int world, int rank, long long count, void *stream);
+
 /* Scratch bytes needed by nnd_query_cuda_f32 (one direction). */
 size_t nnd_query_workspace_bytes(int b, int nq, int nt);
 

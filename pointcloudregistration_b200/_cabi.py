@@ -44,6 +44,10 @@ SIGNATURES = {
                                            c_void_p, c_void_p, c_size_t, c_void_p]),
     "nnd_finalize_cols_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                             c_void_p]),
+    "nnd_peer_max_ranks": (c_int, []),
+    "nnd_exchange_cols_p2p_cuda_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p,
+                                                c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "nnd_sum_p2p_cuda_f32": (c_int, [c_void_p, c_int, c_int, c_longlong, c_void_p]),
     "nnd_profile_enable": (c_int, [c_int]),
     "nnd_profile_collect": (c_int, [c_void_p, c_void_p]),
     "nnd_query_cuda_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,

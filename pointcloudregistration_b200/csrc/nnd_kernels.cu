@@ -1756,6 +1756,72 @@ int nnd_forward_rows_cuda_f32(const float* xyz1, const float* xyz2, int b, int n
                            (cudaStream_t)stream);
 }
 
+int nnd_peer_max_ranks(void) { return kMaxPeers; }
+
+int nnd_exchange_cols_p2p_cuda_f32(const void* const* peer_colkeys, void* const* peer_dist1, void* const* peer_idx1,
+                                   void* const* peer_dist2, void* const* peer_idx2, int world, int rank, const float* xyz1,
+                                   const float* xyz2, int b, int n, int m, int row_lo, int row_hi, void* stream) {
+  g_launches = 0;
+  if (!sizes_ok(b, n, m) || b == 0 || n == 0 || m == 0) return NND_EINVAL;
+  if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world) return NND_EINVAL;
+  if (row_lo < 0 || row_hi < row_lo || row_hi > n) return NND_EINVAL;
+  if (!peer_colkeys || !peer_dist1 || !peer_idx1 || !peer_dist2 || !peer_idx2 || !xyz1 || !xyz2) return NND_EINVAL;
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  ExchangeParams ep{};
+  for (int r = 0; r < world; ++r) {
+    if (!peer_colkeys[r] || !peer_dist1[r] || !peer_idx1[r] || !peer_dist2[r] || !peer_idx2[r]) return NND_EINVAL;
+    ep.keys[r] = (const unsigned long long*)peer_colkeys[r];
+    ep.dist1[r] = (float*)peer_dist1[r];
+    ep.idx1[r] = (int32_t*)peer_idx1[r];
+    ep.dist2[r] = (float*)peer_dist2[r];
+    ep.idx2[r] = (int32_t*)peer_idx2[r];
+  }
+  ep.fc = FinColParams{nullptr, xyz1, xyz2, nullptr, nullptr, n, m, tiles_of(m), (long long)b * m, 1.0f, m, 0};
+  ep.world = world;
+  ep.rank = rank;
+  const int cs = (m + world - 1) / world;  // columns per rank
+  ep.col_lo = rank * cs < m ? rank * cs : m;
+  ep.col_hi = ep.col_lo + cs < m ? ep.col_lo + cs : m;
+  ep.row_lo = row_lo;
+  ep.row_hi = row_hi;
+  const long long work = (long long)b * ((ep.col_hi - ep.col_lo) > (row_hi - row_lo) ? (ep.col_hi - ep.col_lo) : (row_hi - row_lo));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (kShapes[sym_shape(b, n, m, di.sms)].qpt == kQPT)
+    nnd_exchange_cols_kernel<kTT, kQPT><<<grid_for(work, di.sms), 256, 0, st>>>(ep);
+  else
+    nnd_exchange_cols_kernel<kTT, 2><<<grid_for(work, di.sms), 256, 0, st>>>(ep);
+  ++g_launches;
+  debug_sync("exchange_cols", st);
+  return check_last(cudaGetLastError());
+}
+
+int nnd_sum_p2p_cuda_f32(void* const* peer_bufs, int world, int rank, long long count, void* stream) {
+  g_launches = 0;
+  if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world || count < 0 || !peer_bufs) return NND_EINVAL;
+  if (count == 0) return 0;
+  DeviceInfo di;
+  int rc = device_info(&di);
+  if (rc) return rc;
+  SumParams sp{};
+  for (int r = 0; r < world; ++r) {
+    if (!peer_bufs[r] || ((uintptr_t)peer_bufs[r] & 15u) != 0) return NND_EINVAL;
+    sp.buf[r] = (float*)peer_bufs[r];
+  }
+  sp.world = world;
+  sp.rank = rank;
+  const long long n4 = count / 4, per = (n4 + world - 1) / world;
+  sp.lo4 = rank * per < n4 ? rank * per : n4;
+  sp.hi4 = sp.lo4 + per < n4 ? sp.lo4 + per : n4;
+  sp.tail_lo = rank == world - 1 ? n4 * 4 : count;
+  sp.tail_hi = count;
+  const long long work = sp.hi4 - sp.lo4 > 0 ? sp.hi4 - sp.lo4 : 1;
+  nnd_sum_peers_kernel<<<grid_for(work, di.sms), 256, 0, (cudaStream_t)stream>>>(sp);
+  ++g_launches;
+  return check_last(cudaGetLastError());
+}
+
 int nnd_finalize_cols_cuda_f32(const float* xyz1, const float* xyz2, int b, int n, int m,
                                const unsigned long long* colkeys, float* dist2, int32_t* idx2, void* stream) {
   g_launches = 0;

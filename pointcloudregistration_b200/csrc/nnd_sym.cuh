@@ -284,6 +284,39 @@ __global__ void __launch_bounds__(THREADS, MINB) nnd_scan_sym_kernel(const __gri
 
 // Column finalize: key = (dist_bits << 32 | row group).  Re-evaluate the QPT rows of the group against this
 // column point with the same packed sequence and take the lowest row with d == dist.
+template <int QPT>
+__device__ __forceinline__ void sym_finalize_col(const FinColParams& p, long long batch, int k, unsigned long long key,
+                                                 uint64_t one, float& dist, int32_t& idx) {
+  const float bq = __uint_as_float((unsigned)(key >> 32));
+  const long long j0 = (long long)(unsigned)(key & 0xffffffffull) * QPT;
+  const long long go = batch * p.col_stride + p.col_offset + k;  // position in cols
+  const float* t = p.cols + go * 3;
+  const uint64_t TX = pk2(t[0], t[0]), TY = pk2(t[1], t[1]), TZ = pk2(t[2], t[2]);
+  const float* rows = p.rows + batch * p.n * 3;
+  int found = 0;
+#pragma unroll
+  for (int q = QPT - 2; q >= 0; q -= 2) {  // descending: the last hit is the lowest row
+    long long ja = j0 + q, jb = j0 + q + 1;
+    ja = ja < p.n ? ja : p.n - 1;
+    jb = jb < p.n ? jb : p.n - 1;
+    const float* ra = rows + ja * 3;
+    const float* rb = rows + jb * 3;
+    const uint64_t dd = sqdist2(TX, TY, TZ, pk2(-ra[0], -rb[0]), pk2(-ra[1], -rb[1]), pk2(-ra[2], -rb[2]), one);
+    float lo, hi;
+    upk2(dd, lo, hi);
+    if (hi == bq) found = q + 1;
+    if (lo == bq) found = q;
+  }
+  long long j = j0 + found;
+  j = j < p.n ? j : p.n - 1;
+  // my_lib.cpp:16: the first candidate (row 0) is accepted unconditionally, so a NaN first distance is the answer
+  float first, unused;
+  upk2(sqdist2(TX, TY, TZ, pk2(-rows[0], -rows[0]), pk2(-rows[1], -rows[1]), pk2(-rows[2], -rows[2]), one), first, unused);
+  const bool nan0 = first != first;
+  dist = nan0 ? first : bq;
+  idx = nan0 ? 0 : (int32_t)j;
+}
+
 template <int TT, int QPT>
 __global__ void __launch_bounds__(256) nnd_finalize_cols_kernel(FinColParams p) {
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -292,33 +325,108 @@ __global__ void __launch_bounds__(256) nnd_finalize_cols_kernel(FinColParams p) 
     const long long batch = g / p.m;
     const int k = (int)(g - batch * p.m);
     const unsigned long long key = p.ckeys[batch * p.ttiles * TT + k];
-    const float bq = __uint_as_float((unsigned)(key >> 32));
-    const long long j0 = (long long)(unsigned)(key & 0xffffffffull) * QPT;
-    const long long go = batch * p.col_stride + p.col_offset + k;  // position in cols / dist / idx
-    const float* t = p.cols + go * 3;
-    const uint64_t TX = pk2(t[0], t[0]), TY = pk2(t[1], t[1]), TZ = pk2(t[2], t[2]);
-    const float* rows = p.rows + batch * p.n * 3;
-    int found = 0;
+    const long long go = batch * p.col_stride + p.col_offset + k;  // position in dist / idx
+    sym_finalize_col<QPT>(p, batch, k, key, one, p.dist[go], p.idx[go]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Multi-GPU exchange over PEER MEMORY (NVLink / NVSwitch P2P, buffers from torch's symmetric-memory allocator):
+// the merge of the per-rank column keys, the column finalize and the gather of all results in ONE kernel.
+// Rank r owns a slice of the columns: for each of them it loads the partial key of EVERY rank straight from that
+// rank's memory, takes the integer minimum (order-independent: bit-identical for any world size), resolves it to
+// (dist2, idx2) with the finalize above and stores the result into every rank's output.  The same launch pushes the
+// rank's own rows of dist1 / idx1 to every rank.  Replaces all_reduce(MIN) + replicated finalize + all_gather.
+// The caller brackets the launch with two barriers over all ranks (before: every rank's keys are complete; after:
+// every store has landed).
+constexpr int kMaxPeers = 16;
+struct ExchangeParams {
+  const unsigned long long* keys[kMaxPeers];  // [b][ttiles * TT] per rank
+  float* dist2[kMaxPeers];                    // [b][m]
+  int32_t* idx2[kMaxPeers];
+  float* dist1[kMaxPeers];                    // [b][n]
+  int32_t* idx1[kMaxPeers];
+  FinColParams fc;                            // rows = xyz1, cols = xyz2 (local copies); ckeys / dist / idx unused
+  int world, rank;
+  int col_lo, col_hi;                         // this rank's slice of the columns
+  int row_lo, row_hi;                         // this rank's rows of xyz1 (already final in ITS dist1 / idx1)
+};
+
+template <int TT, int QPT>
+__global__ void __launch_bounds__(256) nnd_exchange_cols_kernel(const __grid_constant__ ExchangeParams p) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t one = pk2(p.fc.one, p.fc.one);
+  const int b = (int)(p.fc.count / p.fc.m);
+  const int ncols = p.col_hi - p.col_lo;
+  for (long long g = first; g < (long long)b * ncols; g += stride) {
+    const long long batch = g / ncols;
+    const int k = p.col_lo + (int)(g - batch * ncols);
+    const long long ko = batch * p.fc.ttiles * TT + k;
+    // all peer loads in flight together (each is a ~2 us round trip over NVLink): predicated, fully unrolled
+    unsigned long long kk[kMaxPeers];
 #pragma unroll
-    for (int q = QPT - 2; q >= 0; q -= 2) {  // descending: the last hit is the lowest row
-      long long ja = j0 + q, jb = j0 + q + 1;
-      ja = ja < p.n ? ja : p.n - 1;
-      jb = jb < p.n ? jb : p.n - 1;
-      const float* ra = rows + ja * 3;
-      const float* rb = rows + jb * 3;
-      const uint64_t dd = sqdist2(TX, TY, TZ, pk2(-ra[0], -rb[0]), pk2(-ra[1], -rb[1]), pk2(-ra[2], -rb[2]), one);
-      float lo, hi;
-      upk2(dd, lo, hi);
-      if (hi == bq) found = q + 1;
-      if (lo == bq) found = q;
+    for (int r = 0; r < kMaxPeers; ++r)
+      kk[r] = r < p.world ? __ldcv(p.keys[r] + ko) : 0xffffffffffffffffull;
+    unsigned long long key = kk[0];
+#pragma unroll
+    for (int r = 1; r < kMaxPeers; ++r) key = kk[r] < key ? kk[r] : key;
+    float d;
+    int32_t i;
+    sym_finalize_col<QPT>(p.fc, batch, k, key, one, d, i);
+    const long long go = batch * p.fc.m + k;
+    for (int r = 0; r < p.world; ++r) {
+      p.dist2[r][go] = d;
+      p.idx2[r][go] = i;
     }
-    long long j = j0 + found;
-    j = j < p.n ? j : p.n - 1;
-    // my_lib.cpp:16: the first candidate (row 0) is accepted unconditionally, so a NaN first distance is the answer
-    float first, unused;
-    upk2(sqdist2(TX, TY, TZ, pk2(-rows[0], -rows[0]), pk2(-rows[1], -rows[1]), pk2(-rows[2], -rows[2]), one), first, unused);
-    const bool nan0 = first != first;
-    p.dist[go] = nan0 ? first : bq;
-    p.idx[go] = nan0 ? 0 : (int32_t)j;
+  }
+  const int nrows = p.row_hi - p.row_lo;
+  const float* own_d = p.dist1[p.rank];
+  const int32_t* own_i = p.idx1[p.rank];
+  for (long long g = first; g < (long long)b * nrows; g += stride) {
+    const long long batch = g / nrows;
+    const long long go = batch * p.fc.n + p.row_lo + (g - batch * nrows);
+    const float d = own_d[go];
+    const int32_t i = own_i[go];
+    for (int r = 0; r < p.world; ++r)
+      if (r != p.rank) {
+        p.dist1[r][go] = d;
+        p.idx1[r][go] = i;
+      }
+  }
+}
+
+// Sum of the per-rank gradient buffers over peer memory, two-shot: rank r adds up its slice of EVERY rank's buffer in
+// rank order (the same bits on every rank, run to run) and stores the sum into every rank's buffer.  Slice r is read and
+// written by rank r only, so the exchange is in place.  Bracketed by two barriers like the column exchange.
+struct SumParams {
+  float* buf[kMaxPeers];
+  int world, rank;
+  long long lo4, hi4;  // this rank's slice in float4 units
+  long long tail_lo, tail_hi;  // scalar leftovers (the last rank takes them)
+};
+__global__ void __launch_bounds__(256) nnd_sum_peers_kernel(const __grid_constant__ SumParams p) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  for (long long i = p.lo4 + first; i < p.hi4; i += stride) {
+    float4 v[kMaxPeers];  // all peer loads in flight together; summed in rank order
+#pragma unroll
+    for (int r = 0; r < kMaxPeers; ++r)
+      v[r] = r < p.world ? __ldcv(reinterpret_cast<const float4*>(p.buf[r]) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 acc = v[0];
+#pragma unroll
+    for (int r = 1; r < kMaxPeers; ++r)
+      if (r < p.world) {
+        acc.x += v[r].x;
+        acc.y += v[r].y;
+        acc.z += v[r].z;
+        acc.w += v[r].w;
+      }
+    for (int r = 0; r < p.world; ++r) reinterpret_cast<float4*>(p.buf[r])[i] = acc;
+  }
+  for (long long i = p.tail_lo + first; i < p.tail_hi; i += stride) {
+    float acc = p.buf[0][i];
+    for (int r = 1; r < p.world; ++r) acc += p.buf[r][i];
+    for (int r = 0; r < p.world; ++r) p.buf[r][i] = acc;
   }
 }

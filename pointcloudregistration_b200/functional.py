@@ -256,12 +256,14 @@ def row_group() -> int:
     return int(_cabi.load().nnd_row_group())
 
 
-def nnd_forward_rows_raw(xyz1: torch.Tensor, xyz2: torch.Tensor, row_lo: int, row_hi: int):
+def nnd_forward_rows_raw(xyz1: torch.Tensor, xyz2: torch.Tensor, row_lo: int, row_hi: int, out=None):
     """Symmetric forward over rows [row_lo, row_hi) of xyz1 (include/nnd_b200.h: nnd_forward_rows_cuda_f32).
 
     Returns (dist1 [B, rows] f32, idx1 [B, rows] int32, colkeys [B * nnd_colkeys_count(1, M)] int64): the rows'
     final results and the packed per-column partial results, to be merged across ranks with an integer MIN and
-    resolved by nnd_finalize_cols_raw."""
+    resolved by nnd_finalize_cols_raw.
+    out (optional): (dist1 [B, N] f32, idx1 [B, N] int32, colkeys int64) caller-owned FULL-SIZE buffers to write into
+    (the multi-GPU path passes peer-addressable memory, sharded.PeerExchange)."""
     _check_clouds(xyz1, xyz2)
     lib = _cabi.load()
     xyz1 = xyz1.contiguous()
@@ -271,10 +273,19 @@ def nnd_forward_rows_raw(xyz1: torch.Tensor, xyz2: torch.Tensor, row_lo: int, ro
     dev = xyz1.device
     if b == 0 or n == 0 or m == 0:
         raise ValueError("nnd_forward_rows_raw needs non-empty clouds")
-    dist1 = torch.empty(b, n, dtype=torch.float32, device=dev)
-    idx1 = torch.empty(b, n, dtype=torch.int32, device=dev)
+    if out is not None:
+        dist1, idx1, colkeys = out
+        if (dist1.shape != (b, n) or idx1.shape != (b, n) or dist1.dtype != torch.float32 or idx1.dtype != torch.int32
+                or colkeys.dtype != torch.int64 or colkeys.numel() != lib.nnd_colkeys_count(b, m)
+                or not (dist1.is_contiguous() and idx1.is_contiguous() and colkeys.is_contiguous())
+                or dist1.device != dev or idx1.device != dev or colkeys.device != dev):
+            raise ValueError("nnd_forward_rows_raw: `out` buffers have the wrong shape, dtype or device")
+    else:
+        dist1 = torch.empty(b, n, dtype=torch.float32, device=dev)
+        idx1 = torch.empty(b, n, dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
-        colkeys = torch.empty(lib.nnd_colkeys_count(b, m), dtype=torch.int64, device=dev)
+        if out is None:
+            colkeys = torch.empty(lib.nnd_colkeys_count(b, m), dtype=torch.int64, device=dev)
         ws = _workspace(lib.nnd_rows_workspace_bytes(b, n, m), dev)
         rc = lib.nnd_forward_rows_cuda_f32(xyz1.data_ptr(), xyz2.data_ptr(), b, n, m, int(row_lo), int(row_hi),
                                            dist1.data_ptr(), idx1.data_ptr(), colkeys.data_ptr(), ws.data_ptr(),

@@ -31,6 +31,7 @@ inject the oracle there to exercise this host logic without a GPU.
 """
 from __future__ import annotations
 
+import os
 from dataclasses import dataclass
 
 import torch
@@ -101,14 +102,16 @@ class CudaCompute:
 
         return row_group()
 
+    supports_peer_exchange = True  # rows() can write into caller-owned (peer-addressable) buffers
+
     @staticmethod
-    def rows(xyz1: torch.Tensor, xyz2: torch.Tensor, lo: int, hi: int):
+    def rows(xyz1: torch.Tensor, xyz2: torch.Tensor, lo: int, hi: int, out=None):
         """(dist1 [B,hi-lo], idx1 [B,hi-lo], colkeys int64) for rows [lo, hi) of xyz1 against all of xyz2."""
         from .functional import nnd_forward_rows_raw
 
-        out = nnd_forward_rows_raw(xyz1, xyz2, lo, hi)
+        res = nnd_forward_rows_raw(xyz1, xyz2, lo, hi, out=out)
         CudaCompute._count()
-        return out
+        return res
 
     @staticmethod
     def finalize_cols(xyz1: torch.Tensor, xyz2: torch.Tensor, colkeys: torch.Tensor):
@@ -149,6 +152,110 @@ class CudaCompute:
         out = nnd_backward_raw(xyz1, xyz2, graddist1, graddist2, idx1, idx2, exact=True)
         CudaCompute._count()
         return out
+
+
+#: False = always the NCCL collectives (A/B measurements; NND_B200_PEER_EXCHANGE=0 in the environment does the same)
+peer_exchange = os.environ.get("NND_B200_PEER_EXCHANGE", "1") != "0"
+
+
+class PeerExchange:
+    """The exchange steps of one (group, device, B, N, M) problem over PEER MEMORY instead of NCCL collectives
+    (include/nnd_b200.h: nnd_exchange_cols_p2p_cuda_f32, nnd_sum_p2p_cuda_f32; csrc/nnd_sym.cuh).
+
+    Every rank keeps its column keys, dist1 / idx1, dist2 / idx2 and the flat gradient buffer in ONE symmetric-memory
+    allocation (torch.distributed._symmetric_memory: the same virtual layout on every rank, every rank can address every
+    other rank's copy over NVLink / NVSwitch).  forward: the rows kernel writes straight into it; then barrier, ONE kernel
+    (merge of the column keys + column finalize of the own slice + stores of dist2 / idx2 and of the own rows of
+    dist1 / idx1 into every rank), barrier.  backward: the gradient terms accumulate into the flat buffer; barrier, ONE
+    kernel (two-shot sum in rank order), barrier.  The barriers are torch's symmetric-memory barrier on the current stream.
+    Results: the same bits as the NCCL formulation (an integer minimum; the sum is in rank order, identical on every
+    rank)."""
+
+    _cache: dict = {}
+    _unavailable = False
+
+    @classmethod
+    def get(cls, xyz1, xyz2, group, world, rank, compute):
+        if (not peer_exchange or cls._unavailable or world < 2 or not xyz1.is_cuda
+                or not getattr(compute, "supports_peer_exchange", False)):
+            return None
+        b, n, m = xyz1.size(0), xyz1.size(1), xyz2.size(1)
+        key = (id(group) if group is not None else 0, xyz1.device.index, b, n, m, world)
+        px = cls._cache.get(key)
+        if px is None:
+            try:
+                px = cls(xyz1.device, group, world, rank, b, n, m)
+            except Exception as exc:  # noqa: BLE001 -- no symmetric memory on this box / backend: NCCL collectives it is
+                import sys
+
+                cls._unavailable = True
+                print(f"[nnd_b200] peer-memory exchange unavailable ({type(exc).__name__}: {str(exc)[:200]}); "
+                      "using NCCL collectives", file=sys.stderr)
+                return None
+            cls._cache[key] = px
+        return px
+
+    def __init__(self, dev, group, world, rank, b, n, m):
+        import ctypes
+
+        import torch.distributed._symmetric_memory as symm_mem
+
+        from . import _cabi
+
+        lib = _cabi.load()
+        if world > lib.nnd_peer_max_ranks():
+            raise RuntimeError(f"at most {lib.nnd_peer_max_ranks()} ranks")
+        self.lib, self.dev, self.world, self.rank, self.b, self.n, self.m = lib, dev, world, rank, b, n, m
+        cc = int(lib.nnd_colkeys_count(b, m))
+        parts = (("colkeys", cc * 8), ("dist1", b * n * 4), ("idx1", b * n * 4), ("dist2", b * m * 4), ("idx2", b * m * 4),
+                 ("flat", 3 * b * (n + m) * 4))
+        offs, total = {}, 0
+        for name, nbytes in parts:
+            offs[name] = total
+            total += -(-nbytes // 256) * 256
+        self.buf = symm_mem.empty(total, dtype=torch.uint8, device=dev)
+        self.hdl = symm_mem.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        bases = [int(p_) for p_ in self.hdl.buffer_ptrs]
+        self.ptrs = {name: (ctypes.c_void_p * world)(*[base + off for base in bases]) for name, off in offs.items()}
+
+        def view(name, nbytes, dtype, shape):
+            return self.buf[offs[name]:offs[name] + nbytes].view(dtype).view(shape)
+
+        self.colkeys = view("colkeys", cc * 8, torch.int64, (cc,))
+        self.dist1 = view("dist1", b * n * 4, torch.float32, (b, n))
+        self.idx1 = view("idx1", b * n * 4, torch.int32, (b, n))
+        self.dist2 = view("dist2", b * m * 4, torch.float32, (b, m))
+        self.idx2 = view("idx2", b * m * 4, torch.int32, (b, m))
+        self.flat = view("flat", 3 * b * (n + m) * 4, torch.float32, (3 * b * (n + m),))
+
+    def exchange_cols(self, xyz1, xyz2, lo1: int, hi1: int) -> None:
+        """After rows() wrote this rank's keys and rows into the buffers: every rank ends up with all of dist1, idx1,
+        dist2, idx2."""
+        from . import _cabi
+        from .functional import _stream_ptr
+
+        self.hdl.barrier(channel=0)  # every rank's rows kernel is done: its keys are complete
+        with torch.cuda.device(self.dev):
+            rc = self.lib.nnd_exchange_cols_p2p_cuda_f32(self.ptrs["colkeys"], self.ptrs["dist1"], self.ptrs["idx1"],
+                                                         self.ptrs["dist2"], self.ptrs["idx2"], self.world, self.rank,
+                                                         xyz1.data_ptr(), xyz2.data_ptr(), self.b, self.n, self.m,
+                                                         int(lo1), int(hi1), _stream_ptr(self.dev))
+        _cabi.check(rc, "nnd_exchange_cols_p2p_cuda_f32")
+        CudaCompute._count()
+        self.hdl.barrier(channel=0)  # every rank's stores have landed (and nobody rewrites its keys before all have read)
+
+    def sum_flat(self) -> None:
+        """In-place sum of every rank's flat gradient buffer (rank order: the same bits everywhere)."""
+        from . import _cabi
+        from .functional import _stream_ptr
+
+        self.hdl.barrier(channel=1)
+        with torch.cuda.device(self.dev):
+            rc = self.lib.nnd_sum_p2p_cuda_f32(self.ptrs["flat"], self.world, self.rank, self.flat.numel(),
+                                               _stream_ptr(self.dev))
+        _cabi.check(rc, "nnd_sum_p2p_cuda_f32")
+        CudaCompute._count()
+        self.hdl.barrier(channel=1)
 
 
 def _world(group):
@@ -219,6 +326,15 @@ def sharded_forward(xyz1, xyz2, group=None, src=None, gather=True, compute=CudaC
                                                                           device=xyz1.device))
         (d1, i1), (d2, i2) = z(n if gather else hi1 - lo1), z(m if gather else hi2 - lo2)
         return d1, d2, i1, i2, info
+    px = PeerExchange.get(xyz1, xyz2, group, world, rank, compute) if gather else None
+    if px is not None:  # the exchange over peer memory: one kernel instead of all_reduce + finalize + all_gather
+        compute.rows(xyz1.contiguous(), xyz2.contiguous(), lo1, hi1, out=(px.dist1, px.idx1, px.colkeys))
+        _mark("rows kernel (prepare + scan + finalize rows)", xyz1)
+        px.exchange_cols(xyz1.contiguous(), xyz2.contiguous(), lo1, hi1)
+        _mark("peer-memory exchange: barrier, merge + column finalize + stores to every rank (one kernel), barrier", xyz1)
+        out = px.dist1.clone(), px.dist2.clone(), px.idx1.clone(), px.idx2.clone()  # the buffers are reused by the next call
+        _mark("copies of the four results out of the exchange buffers", xyz1)
+        return out[0], out[1], out[2], out[3], info
     d1, i1, colkeys = compute.rows(xyz1, xyz2, lo1, hi1)
     _mark("rows kernel (prepare + scan + finalize rows)", xyz1)
     pending = None
@@ -266,8 +382,13 @@ def sharded_backward(xyz1, xyz2, graddist1, graddist2, idx1, idx2, info: ShardIn
     if gathered:
         graddist1, idx1 = graddist1[:, lo1:hi1], idx1[:, lo1:hi1]
         graddist2, idx2 = graddist2[:, lo2:hi2], idx2[:, lo2:hi2]
-    # one flat buffer for both gradients: a single all_reduce instead of two
-    flat = torch.zeros(xyz1.numel() + xyz2.numel(), dtype=xyz1.dtype, device=xyz1.device)
+    # one flat buffer for both gradients: a single all_reduce (or one peer-memory sum) instead of two
+    px = PeerExchange.get(xyz1, xyz2, group, info.world, info.rank, compute) if info.world > 1 else None
+    if px is not None:
+        flat = px.flat
+        flat.zero_()
+    else:
+        flat = torch.zeros(xyz1.numel() + xyz2.numel(), dtype=xyz1.dtype, device=xyz1.device)
     g1 = flat[:xyz1.numel()].view_as(xyz1)
     g2 = flat[xyz1.numel():].view_as(xyz2)
     if xyz1.size(0) == 1:
@@ -283,6 +404,10 @@ def sharded_backward(xyz1, xyz2, graddist1, graddist2, idx1, idx2, info: ShardIn
         g1[:, lo1:hi1] += own1
         g2[:, lo2:hi2] += own2
     _mark("backward: zero-fill + both gradient terms", xyz1)
+    if px is not None:
+        px.sum_flat()
+        _mark("peer-memory sum of the gradients: barrier, two-shot sum (one kernel), barrier", xyz1)
+        return g1.clone(), g2.clone()  # the exchange buffer is reused by the next call
     if info.world > 1:
         dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
         _mark("all_reduce(SUM) gradients", xyz1)
