@@ -903,8 +903,11 @@ def run_b200_arm(args, w):
             "config": config_of(w),
             "config_detail": {"pairs_per_step": pairs, "l2": "256 MB buffer rewritten between timed steps (L2 flush)",
                               "parallelism": "xyz1 rows sharded over ranks (symmetric scan: each rank evaluates its rows x "
-                                             "all columns once); NCCL broadcast of both clouds, int64 MIN all_reduce of "
-                                             "the column keys, all_gather of dist1/idx1, SUM all_reduce of gradients; "
+                                             "all columns once); NCCL broadcast of both clouds; exchange over peer memory "
+                                             "(NVLink P2P, torch symmetric memory): one kernel merges the column keys, "
+                                             "finalizes the own slice and stores dist/idx into every rank, one kernel sums "
+                                             "the gradients (NCCL int64 MIN all_reduce + all_gather + SUM all_reduce when "
+                                             "symmetric memory is unavailable or NND_B200_PEER_EXCHANGE=0); "
                                              "e2e: every rank uploads the inputs from its own pinned host copy (no "
                                              "broadcast), rank 0 downloads the gradients and the loss"
                                              if world > 1 else "single GPU"},

@@ -22,9 +22,10 @@ Forward results are bit-identical for any G: row results are a pure per-row func
 key (dist_bits << 32 | row_group) is an order-independent integer minimum.  Gradients differ from
 the 1-GPU result only by fp32 summation order (within the 1e-5 contract).
 
-The collectives are plain NCCL calls: at N=M=1M they move ~60 MB per step against >= 35 ms of
-compute per GPU at G=8, i.e. ~1 % of the step, so a fused compute+collective kernel has nothing to
-overlap (numbers in DESIGN.md).
+On CUDA with torch's symmetric memory the exchange steps run over PEER MEMORY (class PeerExchange below): the merge of
+the column keys, the column finalize and the gather of all results are ONE kernel per rank, the gradient sum another
+(include/nnd_b200.h: nnd_exchange_cols_p2p_cuda_f32, nnd_sum_p2p_cuda_f32).  The NCCL collectives listed above are the
+fallback (no symmetric memory, the CPU tests, NND_B200_PEER_EXCHANGE=0); both give the same bits (numbers in DESIGN.md 5).
 
 `compute` is the per-rank engine.  The product default is the CUDA C ABI; the CPU `gloo` tests
 inject the oracle there to exercise this host logic without a GPU.
