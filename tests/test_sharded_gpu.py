@@ -198,7 +198,19 @@ def _nccl_worker(rank, world, port, b, n, m, out):
         d1, d2, i1, i2 = sharded.nnd_sharded_with_idx(a, c, src=0)
         gd1, gd2 = synthetic.grad_pair(b, n, m, 71)
         ((d1 * gd1.to(dev)).sum() + (d2 * gd2.to(dev)).sum()).backward()
-        torch.save({k: v.detach().cpu() for k, v in dict(d1=d1, d2=d2, i1=i1, i2=i2, g1=a.grad, g2=c.grad).items()},
+        used_peer_memory = len(sharded.PeerExchange._cache) > 0
+        # the same step through the NCCL collectives: the forward must agree bit for bit, the gradients to rounding
+        sharded.peer_exchange = False
+        a2 = a.detach().clone().requires_grad_(True)
+        c2 = c.detach().clone().requires_grad_(True)
+        e1, e2, j1, j2 = sharded.nnd_sharded_with_idx(a2, c2, src=0)
+        ((e1 * gd1.to(dev)).sum() + (e2 * gd2.to(dev)).sum()).backward()
+        sharded.peer_exchange = True
+        same_forward = all(bool(torch.equal(p_, q_)) for p_, q_ in ((d1, e1), (d2, e2), (i1, j1), (i2, j2)))
+        scale = float(max(a2.grad.abs().max(), c2.grad.abs().max()))
+        grad_gap = float(max((a.grad - a2.grad).abs().max(), (c.grad - c2.grad).abs().max())) / scale
+        torch.save(dict(d1=d1.detach().cpu(), d2=d2.detach().cpu(), i1=i1.cpu(), i2=i2.cpu(), g1=a.grad.cpu(), g2=c.grad.cpu(),
+                        used_peer_memory=used_peer_memory, same_forward=same_forward, grad_gap=grad_gap),
                    f"{out}/r{rank}.pt")
     finally:
         dist.destroy_process_group()
@@ -222,3 +234,8 @@ def test_two_ranks_nccl(cuda_lib, tmp_path):
         z = torch.load(f"{tmp_path}/r{r}.pt")
         assert_forward_exact(tuple(z[k].numpy() for k in ("d1", "d2", "i1", "i2")), want, what=f"rank {r}: ")
         assert_grad_close((z["g1"].numpy(), z["g2"].numpy()), wg, what=f"rank {r}: ")
+        # the exchange over peer memory (when this box has symmetric memory) and the NCCL collectives agree
+        assert z["same_forward"] and z["grad_gap"] <= 1e-5, (r, z["used_peer_memory"], z["grad_gap"])
+    z0, z1 = torch.load(f"{tmp_path}/r0.pt"), torch.load(f"{tmp_path}/r1.pt")
+    if z0["used_peer_memory"]:  # the two-shot sum runs in rank order: the same gradient bits on every rank
+        assert torch.equal(z0["g1"], z1["g1"]) and torch.equal(z0["g2"], z1["g2"])
