@@ -113,3 +113,19 @@ def test_packaging_metadata_names_the_drop_in_modules():
     for name in ("pointcloudregistration_b200", "torch_nndistance", "torch_nndistance_aten", "libnnd_b200.so"):
         assert name in text
     assert "build_library" in (ROOT / "setup.py").read_text()
+
+
+def test_peer_exchange_is_cuda_only_and_validates_without_a_gpu(cuda_lib):
+    """The exchange over peer memory needs CUDA tensors (the CPU `gloo` tests keep the collectives); its C entry points
+    reject bad rank / world / pointer arguments before touching a device."""
+    import torch
+
+    from pointcloudregistration_b200 import sharded
+
+    x = torch.zeros(1, 16, 3)
+    assert sharded.PeerExchange.get(x, x, None, 2, 0, sharded.CudaCompute) is None
+    assert cuda_lib.nnd_peer_max_ranks() >= 8
+    assert cuda_lib.nnd_sum_p2p_cuda_f32(None, 2, 0, 16, None) == 10001
+    assert cuda_lib.nnd_sum_p2p_cuda_f32(None, 0, 0, 16, None) == 10001
+    assert cuda_lib.nnd_exchange_cols_p2p_cuda_f32(None, None, None, None, None, 2, 5, None, None, 1, 8, 8, 0, 8, None) == 10001
+    assert cuda_lib.nnd_exchange_cols_p2p_cuda_f32(None, None, None, None, None, 99, 0, None, None, 1, 8, 8, 0, 8, None) == 10001
