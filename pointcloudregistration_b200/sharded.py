@@ -184,13 +184,20 @@ class PeerExchange:
         key = (id(group) if group is not None else 0, xyz1.device.index, b, n, m, world)
         px = cls._cache.get(key)
         if px is None:
+            why = None
             try:
                 px = cls(xyz1.device, group, world, rank, b, n, m)
             except Exception as exc:  # noqa: BLE001 -- no symmetric memory on this box / backend: NCCL collectives it is
+                why = f"{type(exc).__name__}: {str(exc)[:200]}"
+            # every rank takes the same path: one rank without the buffers sends ALL ranks to the collectives (a rank
+            # waiting at a peer-memory barrier for one that went to NCCL would never return).  First use only.
+            ok = torch.tensor([0 if px is None else 1], dtype=torch.int32, device=xyz1.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if int(ok.item()) == 0:
                 import sys
 
                 cls._unavailable = True
-                print(f"[nnd_b200] peer-memory exchange unavailable ({type(exc).__name__}: {str(exc)[:200]}); "
+                print(f"[nnd_b200] peer-memory exchange unavailable ({why or 'another rank could not set it up'}); "
                       "using NCCL collectives", file=sys.stderr)
                 return None
             cls._cache[key] = px
