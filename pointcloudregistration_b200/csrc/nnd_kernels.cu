@@ -250,7 +250,7 @@ __global__ void __launch_bounds__(256) nnd_finalize_kernel(FinParams p) {
       const float x = -qp[0], y = -qp[1], z = -qp[2];
       const int mybatch = (int)batch;
       int myfound = 0;
-#pragma unroll 1
+#pragma unroll 4  // four rows' loads in flight: the loop is latency-bound (ncu: long scoreboard 4.2 per issue at unroll 1)
       for (int it = 0; it < 32 / R; ++it) {
         const int r = it * R + grp;  // the row (lane index inside the warp) this lane group works on
         const unsigned long long rkey = __shfl_sync(FULL, key, r);
